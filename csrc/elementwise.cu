@@ -1,0 +1,397 @@
+// Bandwidth-bound kernels: embedding gather/scatter, RMSNorm fwd/bwd, dropout+residual, rotary,
+// SwiGLU.  Each is a single pass with 128-bit accesses; the reference issues 6-12 ATen launches for
+// the same math.  Where a GEMM epilogue already fuses the op
+// (B200_EPI_ROPE_BF16 / RESID_DROPOUT / SWIGLU*) the kernel here is the unfused companion used for
+// validation and for the layouts the epilogues do not cover.
+#include <cuda_bf16.h>
+
+#include "../include/b200_trainer.h"
+#include "common/host.h"
+#include "common/philox.cuh"
+#include "common/ptx.cuh"
+
+namespace b200 {
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+__device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
+  asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w)
+               : "memory");
+}
+
+// ------------------------------------------------------------------------------------------------ embedding
+// one warp per token row; hidden % 8 == 0
+__global__ void embed_fwd_kernel(const int64_t* __restrict__ ids, const __nv_bfloat16* __restrict__ w,
+                                 float* __restrict__ out, int rows, int hidden, int vocab) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  long long id = ids[row];
+  id = id < 0 ? 0 : (id >= vocab ? vocab - 1 : id);
+  const uint4* src = reinterpret_cast<const uint4*>(w + size_t(id) * hidden);
+  float4* dst = reinterpret_cast<float4*>(out + size_t(row) * hidden);
+  for (int i = lane_id(); i < hidden / 8; i += 32) {
+    const uint4 q = src[i];
+    const float2 a = unpack_bf16x2(q.x), b = unpack_bf16x2(q.y), c = unpack_bf16x2(q.z), d = unpack_bf16x2(q.w);
+    dst[2 * i] = make_float4(a.x, a.y, b.x, b.y);
+    dst[2 * i + 1] = make_float4(c.x, c.y, d.x, d.y);
+  }
+}
+
+__global__ void embed_bwd_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dx,
+                                 float* __restrict__ dw, int rows, int hidden, int vocab) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  long long id = ids[row];
+  if (id < 0 || id >= vocab) return;
+  const float4* src = reinterpret_cast<const float4*>(dx + size_t(row) * hidden);
+  float* dst = dw + size_t(id) * hidden;
+  for (int i = lane_id(); i < hidden / 4; i += 32) red_add_v4(dst + 4 * i, src[i]);
+}
+
+// ------------------------------------------------------------------------------------------------ RMSNorm
+// one warp per row, two reads of the row (the second hits L1).  hidden % 8 == 0.
+__global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w,
+                                   __nv_bfloat16* __restrict__ y, float* __restrict__ rstd, int rows, int hidden,
+                                   float eps) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const float4* xr = reinterpret_cast<const float4*>(x + size_t(row) * hidden);
+  float ss = 0.f;
+  for (int i = lane_id(); i < hidden / 4; i += 32) {
+    const float4 v = xr[i];
+    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+  }
+  ss = warp_sum(ss);
+  const float r = rsqrtf(ss / float(hidden) + eps);
+  if (lane_id() == 0) rstd[row] = r;
+  const uint4* wr = reinterpret_cast<const uint4*>(w);
+  uint4* yr = reinterpret_cast<uint4*>(y + size_t(row) * hidden);
+  for (int i = lane_id(); i < hidden / 8; i += 32) {
+    const float4 a = xr[2 * i], b = xr[2 * i + 1];
+    const uint4 wq = wr[i];
+    const float2 w0 = unpack_bf16x2(wq.x), w1 = unpack_bf16x2(wq.y), w2 = unpack_bf16x2(wq.z), w3 = unpack_bf16x2(wq.w);
+    uint4 o;
+    o.x = pack_bf16x2(a.x * r * w0.x, a.y * r * w0.y);
+    o.y = pack_bf16x2(a.z * r * w1.x, a.w * r * w1.y);
+    o.z = pack_bf16x2(b.x * r * w2.x, b.y * r * w2.y);
+    o.w = pack_bf16x2(b.z * r * w3.x, b.w * r * w3.y);
+    yr[i] = o;
+  }
+}
+
+// Backward.  With g = dy*w, r = rstd:  dx += r*g - x * r^3 * mean(g*x) ;  dw += sum_rows dy * x * r.
+// Persistent warps stride over rows and keep their dw partials in registers (columns owned by a lane
+// are fixed), then one smem reduction + one red.add per column per CTA.
+constexpr int kNormMaxVec = 8;  // 8 x (8 columns) x 32 lanes = 2048 columns max
+__global__ void __launch_bounds__(256)
+rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x,
+                   const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd, float* __restrict__ dx,
+                   float* __restrict__ dw, int rows, int hidden) {
+  extern __shared__ float s_dw[];  // [hidden]
+  for (int i = threadIdx.x; i < hidden; i += blockDim.x) s_dw[i] = 0.f;
+  __syncthreads();
+  const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = lane_id();
+  const int nvec = hidden / 8;
+  float acc[kNormMaxVec][8];
+#pragma unroll
+  for (int k = 0; k < kNormMaxVec; ++k)
+#pragma unroll
+    for (int e = 0; e < 8; ++e) acc[k][e] = 0.f;
+  const uint4* wr = reinterpret_cast<const uint4*>(w);
+  for (int row = blockIdx.x * warps + wid; row < rows; row += gridDim.x * warps) {
+    const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(row) * hidden);
+    const float4* xr = reinterpret_cast<const float4*>(x + size_t(row) * hidden);
+    float4* dxr = reinterpret_cast<float4*>(dx + size_t(row) * hidden);
+    const float r = rstd[row];
+    float dot = 0.f;
+#pragma unroll
+    for (int k = 0; k < kNormMaxVec; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nvec) {
+        const uint4 dq = dyr[i], wq = wr[i];
+        const float4 a = xr[2 * i], b = xr[2 * i + 1];
+        const float xs[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+        const uint32_t dqw[4] = {dq.x, dq.y, dq.z, dq.w}, wqw[4] = {wq.x, wq.y, wq.z, wq.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 d2 = unpack_bf16x2(dqw[e]), w2 = unpack_bf16x2(wqw[e]);
+          dot += d2.x * w2.x * xs[2 * e] + d2.y * w2.y * xs[2 * e + 1];
+          acc[k][2 * e] += d2.x * xs[2 * e] * r;
+          acc[k][2 * e + 1] += d2.y * xs[2 * e + 1] * r;
+        }
+      }
+    }
+    dot = warp_sum(dot);
+    const float coef = dot * r * r * r / float(hidden);
+#pragma unroll
+    for (int k = 0; k < kNormMaxVec; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nvec) {
+        const uint4 dq = dyr[i], wq = wr[i];
+        const float4 a = xr[2 * i], b = xr[2 * i + 1];
+        float4 o0 = dxr[2 * i], o1 = dxr[2 * i + 1];
+        const float2 d0 = unpack_bf16x2(dq.x), d1 = unpack_bf16x2(dq.y), d2 = unpack_bf16x2(dq.z), d3 = unpack_bf16x2(dq.w);
+        const float2 w0 = unpack_bf16x2(wq.x), w1 = unpack_bf16x2(wq.y), w2 = unpack_bf16x2(wq.z), w3 = unpack_bf16x2(wq.w);
+        o0.x += r * d0.x * w0.x - a.x * coef;
+        o0.y += r * d0.y * w0.y - a.y * coef;
+        o0.z += r * d1.x * w1.x - a.z * coef;
+        o0.w += r * d1.y * w1.y - a.w * coef;
+        o1.x += r * d2.x * w2.x - b.x * coef;
+        o1.y += r * d2.y * w2.y - b.y * coef;
+        o1.z += r * d3.x * w3.x - b.z * coef;
+        o1.w += r * d3.y * w3.y - b.w * coef;
+        dxr[2 * i] = o0;
+        dxr[2 * i + 1] = o1;
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < kNormMaxVec; ++k) {
+    const int i = lane + 32 * k;
+    if (i < nvec) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e) atomicAdd(&s_dw[8 * i + e], acc[k][e]);
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < hidden; i += blockDim.x) atomicAdd(&dw[i], s_dw[i]);
+}
+
+// ------------------------------------------------------------------------------------------------ dropout family
+// thread per 8-column group; group index = row * (cols/8) + col/8 (same convention as the GEMM epilogue)
+__global__ void resid_dropout_fwd_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ res,
+                                         float* __restrict__ out, long long groups, float p,
+                                         const unsigned long long* __restrict__ rng, uint32_t stream) {
+  const long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (g >= groups) return;
+  uint32_t keep = 0xFF;
+  float inv = 1.f;
+  if (p > 0.f) {
+    keep = dropout_keep8(rng[0], rng[1], stream, (unsigned long long)g, dropout_threshold16(p));
+    inv = 1.f / (1.f - p);
+  }
+  const uint4 q = reinterpret_cast<const uint4*>(y)[g];
+  const float4 r0 = reinterpret_cast<const float4*>(res)[2 * g], r1 = reinterpret_cast<const float4*>(res)[2 * g + 1];
+  const float2 a = unpack_bf16x2(q.x), b = unpack_bf16x2(q.y), c = unpack_bf16x2(q.z), d = unpack_bf16x2(q.w);
+  const float v[8] = {a.x, a.y, b.x, b.y, c.x, c.y, d.x, d.y};
+  float o[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) o[e] = ((keep >> e) & 1) ? v[e] * inv : 0.f;
+  reinterpret_cast<float4*>(out)[2 * g] = make_float4(r0.x + o[0], r0.y + o[1], r0.z + o[2], r0.w + o[3]);
+  reinterpret_cast<float4*>(out)[2 * g + 1] = make_float4(r1.x + o[4], r1.y + o[5], r1.z + o[6], r1.w + o[7]);
+}
+
+__global__ void dropout_bwd_cast_kernel(const float* __restrict__ dx, __nv_bfloat16* __restrict__ dy, long long groups,
+                                        float p, const unsigned long long* __restrict__ rng, uint32_t stream) {
+  const long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (g >= groups) return;
+  uint32_t keep = 0xFF;
+  float inv = 1.f;
+  if (p > 0.f) {
+    keep = dropout_keep8(rng[0], rng[1], stream, (unsigned long long)g, dropout_threshold16(p));
+    inv = 1.f / (1.f - p);
+  }
+  const float4 a = reinterpret_cast<const float4*>(dx)[2 * g], b = reinterpret_cast<const float4*>(dx)[2 * g + 1];
+  const float v[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
+  float o[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) o[e] = ((keep >> e) & 1) ? v[e] * inv : 0.f;
+  reinterpret_cast<uint4*>(dy)[g] =
+      make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+}
+
+__global__ void dropout_mask_kernel(uint8_t* __restrict__ mask, long long groups, float p,
+                                    const unsigned long long* __restrict__ rng, uint32_t stream) {
+  const long long g = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (g >= groups) return;
+  uint32_t keep = 0xFF;
+  if (p > 0.f) keep = dropout_keep8(rng[0], rng[1], stream, (unsigned long long)g, dropout_threshold16(p));
+#pragma unroll
+  for (int e = 0; e < 8; ++e) mask[8 * g + e] = (keep >> e) & 1;
+}
+
+// ------------------------------------------------------------------------------------------------ rotary
+// thread per (row, head, 8-wide group of the first half); pairs column j with j+32 (head_dim 64)
+__global__ void rope_inplace_kernel(__nv_bfloat16* __restrict__ qkv, const float* __restrict__ cs,
+                                    const float* __restrict__ sn, long long total, int ld, int heads2, int seq,
+                                    int inverse) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int g = int(t & 3);
+  const long long rh = t >> 2;
+  const int head = int(rh % heads2);
+  const long long row = rh / heads2;
+  const int pos = int(row % seq);
+  __nv_bfloat16* base = qkv + row * ld + head * 64 + g * 8;
+  const uint4 lo = *reinterpret_cast<const uint4*>(base), hi = *reinterpret_cast<const uint4*>(base + 32);
+  const float4 c0 = reinterpret_cast<const float4*>(cs + size_t(pos) * 32)[2 * g], c1 = reinterpret_cast<const float4*>(cs + size_t(pos) * 32)[2 * g + 1];
+  float4 s0 = reinterpret_cast<const float4*>(sn + size_t(pos) * 32)[2 * g], s1 = reinterpret_cast<const float4*>(sn + size_t(pos) * 32)[2 * g + 1];
+  const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+  float ss[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  if (inverse) {
+#pragma unroll
+    for (int e = 0; e < 8; ++e) ss[e] = -ss[e];
+  }
+  const uint32_t low[4] = {lo.x, lo.y, lo.z, lo.w}, hiw[4] = {hi.x, hi.y, hi.z, hi.w};
+  uint32_t ol[4], oh[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 a = unpack_bf16x2(low[e]), b = unpack_bf16x2(hiw[e]);
+    ol[e] = pack_bf16x2(a.x * cc[2 * e] - b.x * ss[2 * e], a.y * cc[2 * e + 1] - b.y * ss[2 * e + 1]);
+    oh[e] = pack_bf16x2(b.x * cc[2 * e] + a.x * ss[2 * e], b.y * cc[2 * e + 1] + a.y * ss[2 * e + 1]);
+  }
+  *reinterpret_cast<uint4*>(base) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+  *reinterpret_cast<uint4*>(base + 32) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+}
+
+// ------------------------------------------------------------------------------------------------ SwiGLU
+__global__ void swiglu_fwd_kernel(const __nv_bfloat16* __restrict__ gu, __nv_bfloat16* __restrict__ act,
+                                  long long groups, int inter) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= groups) return;
+  const int gpr = inter / 8;
+  const long long row = t / gpr;
+  const int c = int(t % gpr) * 8;
+  const uint4 g = *reinterpret_cast<const uint4*>(gu + row * 2 * inter + c);
+  const uint4 u = *reinterpret_cast<const uint4*>(gu + row * 2 * inter + inter + c);
+  const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, uw[4] = {u.x, u.y, u.z, u.w};
+  uint32_t o[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 a = unpack_bf16x2(gw[e]), b = unpack_bf16x2(uw[e]);
+    o[e] = pack_bf16x2(a.x / (1.f + __expf(-a.x)) * b.x, a.y / (1.f + __expf(-a.y)) * b.y);
+  }
+  *reinterpret_cast<uint4*>(act + row * inter + c) = make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+__global__ void swiglu_bwd_kernel(const __nv_bfloat16* __restrict__ dact, const __nv_bfloat16* __restrict__ gu,
+                                  __nv_bfloat16* __restrict__ dgu, long long groups, int inter) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= groups) return;
+  const int gpr = inter / 8;
+  const long long row = t / gpr;
+  const int c = int(t % gpr) * 8;
+  const uint4 g = *reinterpret_cast<const uint4*>(gu + row * 2 * inter + c);
+  const uint4 u = *reinterpret_cast<const uint4*>(gu + row * 2 * inter + inter + c);
+  const uint4 d = *reinterpret_cast<const uint4*>(dact + row * inter + c);
+  const uint32_t gw[4] = {g.x, g.y, g.z, g.w}, uw[4] = {u.x, u.y, u.z, u.w}, dw[4] = {d.x, d.y, d.z, d.w};
+  uint32_t og[4], ou[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {
+    const float2 a = unpack_bf16x2(gw[e]), b = unpack_bf16x2(uw[e]), dd = unpack_bf16x2(dw[e]);
+    const float s0 = 1.f / (1.f + __expf(-a.x)), s1 = 1.f / (1.f + __expf(-a.y));
+    og[e] = pack_bf16x2(dd.x * b.x * s0 * (1.f + a.x * (1.f - s0)), dd.y * b.y * s1 * (1.f + a.y * (1.f - s1)));
+    ou[e] = pack_bf16x2(dd.x * a.x * s0, dd.y * a.y * s1);
+  }
+  *reinterpret_cast<uint4*>(dgu + row * 2 * inter + c) = make_uint4(og[0], og[1], og[2], og[3]);
+  *reinterpret_cast<uint4*>(dgu + row * 2 * inter + inter + c) = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+}
+
+}  // namespace b200
+
+using namespace b200;
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int b200_embed_fwd(const int64_t* ids, const void* w, float* out, int rows, int hidden, int vocab, void* stream) {
+  B200_REQUIRE(hidden % 8 == 0, "embed: hidden %% 8 != 0");
+  embed_fwd_kernel<<<(rows + 7) / 8, 256, 0, STREAM(stream)>>>(ids, (const __nv_bfloat16*)w, out, rows, hidden, vocab);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_embed_bwd(const int64_t* ids, const float* dx, float* dw, int rows, int hidden, int vocab, void* stream) {
+  B200_REQUIRE(hidden % 4 == 0, "embed: hidden %% 4 != 0");
+  embed_bwd_kernel<<<(rows + 7) / 8, 256, 0, STREAM(stream)>>>(ids, dx, dw, rows, hidden, vocab);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_rmsnorm_fwd(const float* x, const void* w, void* y, float* rstd, int rows, int hidden, float eps,
+                     void* stream) {
+  B200_REQUIRE(hidden % 8 == 0, "rmsnorm: hidden %% 8 != 0");
+  rmsnorm_fwd_kernel<<<(rows + 7) / 8, 256, 0, STREAM(stream)>>>(x, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, rstd,
+                                                                  rows, hidden, eps);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_rmsnorm_bwd(const void* dy, const float* x, const void* w, const float* rstd, float* dx, float* dw, int rows,
+                     int hidden, void* stream) {
+  B200_REQUIRE(hidden % 8 == 0 && hidden <= kNormMaxVec * 256, "rmsnorm_bwd: hidden must be a multiple of 8 and <= %d",
+               kNormMaxVec * 256);
+  int grid = sm_count() * 2;
+  const int max_grid = (rows + 7) / 8;
+  if (grid > max_grid) grid = max_grid;
+  rmsnorm_bwd_kernel<<<grid, 256, hidden * sizeof(float), STREAM(stream)>>>(
+      (const __nv_bfloat16*)dy, x, (const __nv_bfloat16*)w, rstd, dx, dw, rows, hidden);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_resid_dropout_fwd(const void* y, const float* res, float* out, int rows, int cols, float p,
+                           const unsigned long long* rng, unsigned int rs, void* stream) {
+  B200_REQUIRE(cols % 8 == 0, "resid_dropout: cols %% 8 != 0");
+  B200_REQUIRE(p == 0.f || rng != nullptr, "resid_dropout: rng_state required when p > 0");
+  const long long groups = (long long)rows * (cols / 8);
+  resid_dropout_fwd_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(
+      (const __nv_bfloat16*)y, res, out, groups, p, rng, rs);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_dropout_bwd_cast(const float* dx, void* dy, int rows, int cols, float p, const unsigned long long* rng,
+                          unsigned int rs, void* stream) {
+  B200_REQUIRE(cols % 8 == 0, "dropout_bwd: cols %% 8 != 0");
+  B200_REQUIRE(p == 0.f || rng != nullptr, "dropout_bwd: rng_state required when p > 0");
+  const long long groups = (long long)rows * (cols / 8);
+  dropout_bwd_cast_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(dx, (__nv_bfloat16*)dy, groups,
+                                                                                         p, rng, rs);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned long long* rng, unsigned int rs,
+                      void* stream) {
+  B200_REQUIRE(cols % 8 == 0, "dropout_mask: cols %% 8 != 0");
+  const long long groups = (long long)rows * (cols / 8);
+  dropout_mask_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(mask, groups, p, rng, rs);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_rope_inplace(void* qkv, const float* cs, const float* sn, int rows, int ld, int rope_cols, int seq_len,
+                      int inverse, void* stream) {
+  B200_REQUIRE(rope_cols % 64 == 0 && ld % 8 == 0, "rope: rope_cols %% 64 / ld %% 8");
+  const int heads2 = rope_cols / 64;
+  const long long total = (long long)rows * heads2 * 4;
+  rope_inplace_kernel<<<(unsigned)((total + 255) / 256), 256, 0, STREAM(stream)>>>((__nv_bfloat16*)qkv, cs, sn, total,
+                                                                                   ld, heads2, seq_len, inverse);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_swiglu_fwd(const void* gu, void* act, int rows, int inter, void* stream) {
+  B200_REQUIRE(inter % 8 == 0, "swiglu: inter %% 8 != 0");
+  const long long groups = (long long)rows * (inter / 8);
+  swiglu_fwd_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>((const __nv_bfloat16*)gu,
+                                                                                  (__nv_bfloat16*)act, groups, inter);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_swiglu_bwd(const void* dact, const void* gu, void* dgu, int rows, int inter, void* stream) {
+  B200_REQUIRE(inter % 8 == 0, "swiglu: inter %% 8 != 0");
+  const long long groups = (long long)rows * (inter / 8);
+  swiglu_bwd_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(
+      (const __nv_bfloat16*)dact, (const __nv_bfloat16*)gu, (__nv_bfloat16*)dgu, groups, inter);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,240 @@
+// Fused softmax cross-entropy (forward + backward in one pass over a logits chunk held in shared
+// memory), fused AdamW with bf16 shadow write, gradient-norm partials, clip coefficient, RNG bump.
+#include <cuda_bf16.h>
+#include <math.h>
+
+#include "../include/b200_trainer.h"
+#include "common/host.h"
+#include "common/ptx.cuh"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------------ cross entropy
+// One CTA per row.  The row (<= ~57k bf16) is staged once in shared memory: global traffic is one read
+// and one write of the chunk, which the chunked LM-head driver keeps L2-resident.
+// Reference: F.cross_entropy(shift_logits, shift_labels) gpt.py:451-453 and its autograd backward.
+constexpr int kCeThreads = 512;
+
+__device__ __forceinline__ float block_reduce(float v, float* scratch, bool is_max) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = is_max ? fmaxf(v, t) : v + t;
+  }
+  __syncthreads();
+  if (lane == 0) scratch[wid] = v;
+  __syncthreads();
+  if (wid == 0) {
+    v = lane < (blockDim.x >> 5) ? scratch[lane] : (is_max ? -INFINITY : 0.f);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float t = __shfl_xor_sync(0xffffffffu, v, o);
+      v = is_max ? fmaxf(v, t) : v + t;
+    }
+    if (lane == 0) scratch[0] = v;
+  }
+  __syncthreads();
+  return scratch[0];
+}
+
+__global__ void __launch_bounds__(kCeThreads)
+ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss_sum,
+                  int vocab, int ld, float loss_scale, float grad_scale) {
+  extern __shared__ __align__(16) uint8_t ce_smem[];
+  uint4* srow = reinterpret_cast<uint4*>(ce_smem);
+  __shared__ float scratch[32];
+  const int row = blockIdx.x;
+  uint4* grow = reinterpret_cast<uint4*>(logits + size_t(row) * ld);
+  const int nvec = ld / 8;
+  const long long label = labels[row];
+  if (label < 0 || label >= vocab) {  // ignored position: zero gradient, no loss
+    for (int i = threadIdx.x; i < nvec; i += blockDim.x) grow[i] = make_uint4(0, 0, 0, 0);
+    return;
+  }
+  float mx = -INFINITY;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 q = grow[i];
+    srow[i] = q;
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = unpack_bf16x2(w[e]);
+      const int c = i * 8 + 2 * e;
+      if (c < vocab) mx = fmaxf(mx, f.x);
+      if (c + 1 < vocab) mx = fmaxf(mx, f.y);
+    }
+  }
+  mx = block_reduce(mx, scratch, true);
+  constexpr float kLog2e = 1.4426950408889634f;
+  const float mxs = mx * kLog2e;
+  float sum = 0.f;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 q = srow[i];
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = unpack_bf16x2(w[e]);
+      const int c = i * 8 + 2 * e;
+      if (c < vocab) sum += exp2f(f.x * kLog2e - mxs);
+      if (c + 1 < vocab) sum += exp2f(f.y * kLog2e - mxs);
+    }
+  }
+  sum = block_reduce(sum, scratch, false);
+  const float inv = grad_scale / sum;
+  if (threadIdx.x == 0) {
+    const float xl = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(srow)[label]);
+    atomicAdd(loss_sum, (logf(sum) + mx - xl) * loss_scale);
+  }
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const uint4 q = srow[i];
+    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+    uint32_t o[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 f = unpack_bf16x2(w[e]);
+      const int c = i * 8 + 2 * e;
+      float g0 = c < vocab ? exp2f(f.x * kLog2e - mxs) * inv : 0.f;
+      float g1 = c + 1 < vocab ? exp2f(f.y * kLog2e - mxs) * inv : 0.f;
+      if (c == label) g0 -= grad_scale;
+      if (c + 1 == label) g1 -= grad_scale;
+      o[e] = pack_bf16x2(g0, g1);
+    }
+    grow[i] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+}
+
+// ------------------------------------------------------------------------------------------------ AdamW
+// torch.optim.AdamW math (decoupled decay; denom = sqrt(v)/sqrt(bc2) + eps), 4 elements per thread.
+__global__ void __launch_bounds__(256)
+adamw_kernel(float* __restrict__ master, const float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
+             __nv_bfloat16* __restrict__ shadow, const uint8_t* __restrict__ decay_chunks, long long lo, long long n4,
+             float lr, float beta1, float beta2, float eps, float wd, float step_size, float inv_sqrt_bc2,
+             const float* __restrict__ grad_scale) {
+  const float gs = grad_scale ? *grad_scale : 1.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const long long gi = lo + 4 * i;  // global flat element index
+    float4 p = *reinterpret_cast<const float4*>(master + gi);
+    float4 g = *reinterpret_cast<const float4*>(grad + gi);
+    float4 mm = reinterpret_cast<const float4*>(m)[i];
+    float4 vv = reinterpret_cast<const float4*>(v)[i];
+    const float decay = decay_chunks[gi >> 7] ? 1.f - lr * wd : 1.f;
+    float* pp = reinterpret_cast<float*>(&p);
+    float* gg = reinterpret_cast<float*>(&g);
+    float* pm = reinterpret_cast<float*>(&mm);
+    float* pv = reinterpret_cast<float*>(&vv);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float ge = gg[e] * gs;
+      pm[e] = beta1 * pm[e] + (1.f - beta1) * ge;
+      pv[e] = beta2 * pv[e] + (1.f - beta2) * ge * ge;
+      const float denom = sqrtf(pv[e]) * inv_sqrt_bc2 + eps;
+      pp[e] = pp[e] * decay - step_size * (pm[e] / denom);
+    }
+    *reinterpret_cast<float4*>(master + gi) = p;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    if (shadow) {
+      uint2 s = make_uint2(pack_bf16x2(pp[0], pp[1]), pack_bf16x2(pp[2], pp[3]));
+      *reinterpret_cast<uint2*>(shadow + gi) = s;
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) sumsq_kernel(const float* __restrict__ x, long long n4, float* __restrict__ out) {
+  float acc = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const float4 a = reinterpret_cast<const float4*>(x)[i];
+    acc += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float s[8];
+  if ((threadIdx.x & 31) == 0) s[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int i = 0; i < 8; ++i) t += s[i];
+    atomicAdd(out, t);
+  }
+}
+
+__global__ void clip_coef_kernel(const float* sumsq, float max_norm, float pre_scale, float* scale, float* norm_out) {
+  // sumsq is of UNSCALED gradients; the norm of the scaled gradient is pre_scale * sqrt(sumsq)
+  const float norm = sqrtf(*sumsq) * fabsf(pre_scale);
+  float c = 1.f;
+  if (max_norm > 0.f) c = fminf(1.f, max_norm / (norm + 1e-6f));
+  *scale = pre_scale * c;
+  if (norm_out) *norm_out = norm;
+}
+
+__global__ void rng_advance_kernel(unsigned long long* st, unsigned long long delta) { st[1] += delta; }
+
+}  // namespace b200
+
+using namespace b200;
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int b200_ce_fwd_bwd(void* logits, const int64_t* labels, float* loss_sum, int rows, int vocab, int ld,
+                    float loss_scale, float grad_scale, void* stream) {
+  B200_REQUIRE(ld % 8 == 0 && ld >= vocab, "ce: ld must be a multiple of 8 and >= vocab");
+  const size_t smem = size_t(ld) * 2;
+  B200_REQUIRE(smem <= 200 * 1024, "ce: a row of %d logits does not fit in shared memory", ld);
+  static size_t configured = 0;
+  if (smem > configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(ce_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    configured = smem;
+  }
+  ce_fwd_bwd_kernel<<<rows, kCeThreads, smem, STREAM(stream)>>>((__nv_bfloat16*)logits, labels, loss_sum, vocab, ld,
+                                                                loss_scale, grad_scale);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_adamw(float* master, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow,
+               const uint8_t* decay_chunks, long long lo, long long hi, int step, float lr, float beta1, float beta2,
+               float eps, float weight_decay, const float* grad_scale, void* stream) {
+  B200_REQUIRE(lo % 4 == 0 && hi % 4 == 0 && hi >= lo, "adamw: range [%lld,%lld) must be 4-element aligned", lo, hi);
+  if (hi == lo) return 0;
+  const long long n4 = (hi - lo) / 4;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  const float step_size = (float)(lr / bc1);
+  const float inv_sqrt_bc2 = (float)(1.0 / sqrt(bc2));
+  long long blocks = (n4 + 255) / 256;
+  const long long cap = (long long)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  adamw_kernel<<<(unsigned)blocks, 256, 0, STREAM(stream)>>>(master, grad, exp_avg, exp_avg_sq, (__nv_bfloat16*)shadow,
+                                                             decay_chunks, lo, n4, lr, beta1, beta2, eps, weight_decay,
+                                                             step_size, inv_sqrt_bc2, grad_scale);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_sumsq(const float* x, long long lo, long long hi, float* out, void* stream) {
+  B200_REQUIRE(lo % 4 == 0 && hi % 4 == 0 && hi >= lo, "sumsq: range must be 4-element aligned");
+  if (hi == lo) return 0;
+  const long long n4 = (hi - lo) / 4;
+  long long blocks = (n4 + 255) / 256;
+  const long long cap = (long long)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  sumsq_kernel<<<(unsigned)blocks, 256, 0, STREAM(stream)>>>(x + lo, n4, out);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_clip_coef(const float* sumsq, float max_norm, float pre_scale, float* scale, float* norm_out, void* stream) {
+  clip_coef_kernel<<<1, 1, 0, STREAM(stream)>>>(sumsq, max_norm, pre_scale, scale, norm_out);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_rng_advance(unsigned long long* st, unsigned long long delta, void* stream) {
+  rng_advance_kernel<<<1, 1, 0, STREAM(stream)>>>(st, delta);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

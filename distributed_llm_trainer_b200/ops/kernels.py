@@ -1,0 +1,208 @@
+"""Python bindings of the C ABI in ``include/b200_trainer.h``: thin, allocation-free wrappers that
+take torch tensors, pass raw device pointers + the current CUDA stream, and raise on any error.
+
+Nothing here falls back to PyTorch: the pure-PyTorch statements of the same ops live in
+``ops/reference.py`` and are used only as test oracles and by CPU-only processes.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Optional
+
+import torch
+
+from . import _lib
+
+EPI_BF16, EPI_F32, EPI_F32_ATOMIC, EPI_ROPE_BF16, EPI_RESID_DROPOUT, EPI_SWIGLU, EPI_SWIGLU_BWD = range(7)
+
+# launch counter: bench.py reports how many of OUR kernels ran inside the timed region
+launch_count = 0
+
+
+class GemmArgs(C.Structure):
+    _fields_ = [
+        ("A", C.c_void_p), ("B", C.c_void_p), ("C", C.c_void_p),
+        ("M", C.c_int), ("N", C.c_int), ("K", C.c_int),
+        ("lda", C.c_int), ("ldb", C.c_int), ("ldc", C.c_int),
+        ("a_mn_major", C.c_int), ("b_mn_major", C.c_int),
+        ("epilogue", C.c_int), ("split_k", C.c_int), ("tile_n", C.c_int), ("max_ctas", C.c_int),
+        ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p), ("seq_len", C.c_int), ("rope_cols", C.c_int),
+        ("residual", C.c_void_p), ("dropout_p", C.c_float), ("rng_state", C.c_void_p), ("rng_stream", C.c_uint),
+        ("aux", C.c_void_p), ("ld_aux", C.c_int), ("half_n", C.c_int),
+    ]
+
+
+_P, _I, _F, _LL, _U = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint
+_SIGS = {
+    "b200_gemm_bf16": [C.POINTER(GemmArgs), _P],
+    "b200_embed_fwd": [_P, _P, _P, _I, _I, _I, _P],
+    "b200_embed_bwd": [_P, _P, _P, _I, _I, _I, _P],
+    "b200_rmsnorm_fwd": [_P, _P, _P, _P, _I, _I, _F, _P],
+    "b200_rmsnorm_bwd": [_P, _P, _P, _P, _P, _P, _I, _I, _P],
+    "b200_resid_dropout_fwd": [_P, _P, _P, _I, _I, _F, _P, _U, _P],
+    "b200_dropout_bwd_cast": [_P, _P, _I, _I, _F, _P, _U, _P],
+    "b200_dropout_mask": [_P, _I, _I, _F, _P, _U, _P],
+    "b200_rope_inplace": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
+    "b200_swiglu_fwd": [_P, _P, _I, _I, _P],
+    "b200_swiglu_bwd": [_P, _P, _P, _I, _I, _P],
+    "b200_attn_fwd": [_P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
+    "b200_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
+    "b200_ce_fwd_bwd": [_P, _P, _P, _I, _I, _I, _F, _F, _P],
+    "b200_adamw": [_P, _P, _P, _P, _P, _P, _LL, _LL, _I, _F, _F, _F, _F, _F, _P, _P],
+    "b200_sumsq": [_P, _LL, _LL, _P, _P],
+    "b200_clip_coef": [_P, _F, _F, _P, _P, _P],
+    "b200_rng_advance": [_P, C.c_ulonglong, _P],
+}
+_fn_cache = {}
+
+
+def _fn(name: str):
+    f = _fn_cache.get(name)
+    if f is None:
+        f = getattr(_lib.lib(), name)
+        f.argtypes = _SIGS[name]
+        f.restype = C.c_int
+        _fn_cache[name] = f
+    return f
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _call(name: str, *args) -> None:
+    global launch_count
+    rc = _fn(name)(*args)
+    if rc != 0:
+        _lib.check(rc, name)
+    launch_count += 1
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+# ----------------------------------------------------------------------------------------------- GEMM
+def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = False, b_mn: bool = False,
+         epilogue: int = EPI_BF16, split_k: int = 1, tile_n: int = 0, max_ctas: int = 0,
+         rope_cos=None, rope_sin=None, seq_len: int = 0, rope_cols: int = 0,
+         residual=None, dropout_p: float = 0.0, rng_state=None, rng_stream: int = 0,
+         aux=None, half_n: int = 0, M: Optional[int] = None, N: Optional[int] = None, K: Optional[int] = None) -> None:
+    """``c = a @ b`` on tcgen05.
+
+    ``a``: K-major ``[M, K]`` or (``a_mn``) MN-major ``[K, M]``; ``b``: K-major ``[N, K]`` or (``b_mn``)
+    MN-major ``[K, N]``.  Row-major 2-D tensors with unit inner stride; leading dimensions come from
+    ``stride(0)`` so column/row slices of packed buffers work without copies.
+    """
+    assert a.dtype == torch.bfloat16 and b.dtype == torch.bfloat16 and a.stride(1) == 1 and b.stride(1) == 1
+    if M is None:
+        M = a.shape[1] if a_mn else a.shape[0]
+    if K is None:
+        K = a.shape[0] if a_mn else a.shape[1]
+    if N is None:
+        N = b.shape[1] if b_mn else b.shape[0]
+    args = GemmArgs(
+        A=a.data_ptr(), B=b.data_ptr(), C=c.data_ptr(), M=M, N=N, K=K,
+        lda=a.stride(0), ldb=b.stride(0), ldc=c.stride(0), a_mn_major=int(a_mn), b_mn_major=int(b_mn),
+        epilogue=epilogue, split_k=split_k, tile_n=tile_n, max_ctas=max_ctas,
+        rope_cos=_ptr(rope_cos), rope_sin=_ptr(rope_sin), seq_len=seq_len, rope_cols=rope_cols,
+        residual=_ptr(residual), dropout_p=dropout_p, rng_state=_ptr(rng_state), rng_stream=rng_stream,
+        aux=_ptr(aux), ld_aux=0 if aux is None else aux.stride(0), half_n=half_n,
+    )
+    _call("b200_gemm_bf16", C.byref(args), _stream())
+
+
+# ----------------------------------------------------------------------------------------------- elementwise
+def embed_fwd(ids, weight_bf16, out_f32):
+    rows = ids.numel()
+    _call("b200_embed_fwd", ids.data_ptr(), weight_bf16.data_ptr(), out_f32.data_ptr(), rows, weight_bf16.shape[1],
+          weight_bf16.shape[0], _stream())
+
+
+def embed_bwd(ids, dx_f32, dweight_f32):
+    rows = ids.numel()
+    _call("b200_embed_bwd", ids.data_ptr(), dx_f32.data_ptr(), dweight_f32.data_ptr(), rows, dweight_f32.shape[1],
+          dweight_f32.shape[0], _stream())
+
+
+def rmsnorm_fwd(x_f32, w_bf16, y_bf16, rstd, eps: float):
+    rows, hidden = x_f32.shape
+    _call("b200_rmsnorm_fwd", x_f32.data_ptr(), w_bf16.data_ptr(), y_bf16.data_ptr(), rstd.data_ptr(), rows, hidden,
+          eps, _stream())
+
+
+def rmsnorm_bwd(dy_bf16, x_f32, w_bf16, rstd, dx_accum, dw_accum):
+    rows, hidden = x_f32.shape
+    _call("b200_rmsnorm_bwd", dy_bf16.data_ptr(), x_f32.data_ptr(), w_bf16.data_ptr(), rstd.data_ptr(),
+          dx_accum.data_ptr(), dw_accum.data_ptr(), rows, hidden, _stream())
+
+
+def resid_dropout_fwd(y_bf16, residual, out, p, rng_state, rng_stream):
+    rows, cols = y_bf16.shape
+    _call("b200_resid_dropout_fwd", y_bf16.data_ptr(), residual.data_ptr(), out.data_ptr(), rows, cols, p,
+          _ptr(rng_state), rng_stream, _stream())
+
+
+def dropout_bwd_cast(dx_f32, dy_bf16, p, rng_state, rng_stream):
+    rows, cols = dx_f32.shape
+    _call("b200_dropout_bwd_cast", dx_f32.data_ptr(), dy_bf16.data_ptr(), rows, cols, p, _ptr(rng_state), rng_stream,
+          _stream())
+
+
+def dropout_mask(mask_u8, p, rng_state, rng_stream):
+    rows, cols = mask_u8.shape
+    _call("b200_dropout_mask", mask_u8.data_ptr(), rows, cols, p, _ptr(rng_state), rng_stream, _stream())
+
+
+def rope_inplace(qkv_bf16, cos, sin, rope_cols, seq_len, inverse=False):
+    rows = qkv_bf16.shape[0]
+    _call("b200_rope_inplace", qkv_bf16.data_ptr(), cos.data_ptr(), sin.data_ptr(), rows, qkv_bf16.stride(0),
+          rope_cols, seq_len, int(inverse), _stream())
+
+
+def swiglu_fwd(gu_bf16, act_bf16):
+    rows, inter = act_bf16.shape
+    _call("b200_swiglu_fwd", gu_bf16.data_ptr(), act_bf16.data_ptr(), rows, inter, _stream())
+
+
+def swiglu_bwd(dact_bf16, gu_bf16, dgu_bf16):
+    rows, inter = dact_bf16.shape
+    _call("b200_swiglu_bwd", dact_bf16.data_ptr(), gu_bf16.data_ptr(), dgu_bf16.data_ptr(), rows, inter, _stream())
+
+
+# ----------------------------------------------------------------------------------------------- attention
+def attn_fwd(qkv_bf16, out_bf16, lse, batch, seq, heads, dropout_p, rng_state, rng_stream):
+    _call("b200_attn_fwd", qkv_bf16.data_ptr(), out_bf16.data_ptr(), lse.data_ptr(), batch, seq, heads, dropout_p,
+          _ptr(rng_state), rng_stream, _stream())
+
+
+def attn_bwd(qkv_bf16, out_bf16, dout_bf16, lse, dqkv_bf16, delta, dq_accum, batch, seq, heads, dropout_p, rng_state,
+             rng_stream):
+    _call("b200_attn_bwd", qkv_bf16.data_ptr(), out_bf16.data_ptr(), dout_bf16.data_ptr(), lse.data_ptr(),
+          dqkv_bf16.data_ptr(), delta.data_ptr(), dq_accum.data_ptr(), batch, seq, heads, dropout_p, _ptr(rng_state),
+          rng_stream, _stream())
+
+
+# ----------------------------------------------------------------------------------------------- loss / optimizer
+def ce_fwd_bwd(logits_bf16, labels, loss_sum, vocab, loss_scale, grad_scale):
+    rows = logits_bf16.shape[0]
+    _call("b200_ce_fwd_bwd", logits_bf16.data_ptr(), labels.data_ptr(), loss_sum.data_ptr(), rows, vocab,
+          logits_bf16.stride(0), loss_scale, grad_scale, _stream())
+
+
+def adamw_step(master, grad, exp_avg, exp_avg_sq, shadow, decay_chunks, lo, hi, step, lr, beta1, beta2, eps, wd,
+               grad_scale):
+    _call("b200_adamw", master.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), _ptr(shadow),
+          decay_chunks.data_ptr(), lo, hi, step, lr, beta1, beta2, eps, wd, _ptr(grad_scale), _stream())
+
+
+def sumsq(x_f32, lo, hi, out):
+    _call("b200_sumsq", x_f32.data_ptr(), lo, hi, out.data_ptr(), _stream())
+
+
+def clip_coef(sumsq_t, max_norm, pre_scale, scale_out, norm_out=None):
+    _call("b200_clip_coef", sumsq_t.data_ptr(), max_norm, pre_scale, scale_out.data_ptr(), _ptr(norm_out), _stream())
+
+
+def rng_advance(rng_state, delta=1):
+    _call("b200_rng_advance", rng_state.data_ptr(), delta, _stream())

@@ -1,0 +1,151 @@
+/* b200_trainer.h -- C ABI of libb200trainer.so (hand-written sm_100a kernels + host runtime).
+ *
+ * Conventions
+ *   - every function returns 0 on success, a negative value on failure; b200_last_error() then
+ *     returns a thread-local message.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = legacy default stream).
+ *   - pointers are device pointers unless stated otherwise; the library never allocates on behalf
+ *     of a kernel: scratch buffers are always caller-provided (see each entry).
+ *   - bf16 tensors are row-major with an explicit leading dimension in ELEMENTS.
+ *   - "reference" citations are paths under the upstream project (zhc180/distributed-llm-trainer).
+ */
+#ifndef B200_TRAINER_H_
+#define B200_TRAINER_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ---------------------------------------------------------------- runtime ------------------- */
+const char* b200_last_error(void);
+int b200_version(void);
+int b200_sm_count(void);
+
+/* Raw device allocations (zero-filled) that can be shared with peer processes through CUDA IPC.
+ * Used for the NVLink communication buffers of the DDP / FSDP engines (reference: the NCCL-internal
+ * buffers behind torch DDP/FSDP, ddp_trainer.py:167-172, fsdp_trainer.py:291-310). */
+int b200_device_malloc(void** ptr, size_t bytes);
+int b200_device_free(void* ptr);
+int b200_ipc_export(void* ptr, void* handle64 /* host, 64 bytes out */);
+int b200_ipc_open(const void* handle64 /* host */, void** ptr);
+int b200_ipc_close(void* ptr);
+int b200_enable_peer_access(int peer_device);
+
+/* ---------------------------------------------------------------- GEMM (tcgen05 / TMEM / TMA) */
+enum {
+  B200_EPI_BF16 = 0,          /* C(bf16) = A*B                                   */
+  B200_EPI_F32 = 1,           /* C(fp32) = A*B                                   */
+  B200_EPI_F32_ATOMIC = 2,    /* C(fp32) += A*B (red.global.add; split-K allowed) */
+  B200_EPI_ROPE_BF16 = 3,     /* C(bf16) = rotary(A*B) on columns [0, rope_cols)  */
+  B200_EPI_RESID_DROPOUT = 4, /* C(fp32) = residual(fp32) + dropout(A*B)          */
+  B200_EPI_SWIGLU = 5,        /* C = [gate|up] (bf16), aux = silu(gate)*up (bf16) */
+  B200_EPI_SWIGLU_BWD = 6     /* C = [dgate|dup] (bf16) from A*B = d_act, aux = [gate|up] */
+};
+
+typedef struct b200_gemm_args {
+  const void* A;  /* bf16. K-major: [M, K] (ld = lda);  MN-major: [K, M] (ld = lda) */
+  const void* B;  /* bf16. K-major: [N, K] (ld = ldb);  MN-major: [K, N] (ld = ldb) */
+  void* C;        /* [M, N] (ld = ldc), dtype per epilogue */
+  int M, N, K;
+  int lda, ldb, ldc;
+  int a_mn_major, b_mn_major;
+  int epilogue;   /* B200_EPI_* */
+  int split_k;    /* <=1: none.  >1 requires B200_EPI_F32_ATOMIC */
+  int tile_n;     /* 128, 256, or 0 = choose by wave efficiency */
+  int max_ctas;   /* 0 = all SMs; otherwise caps the persistent grid (leaves SMs for comm kernels) */
+  /* rotary epilogue: fp32 tables [seq_len, 32] (head_dim 64, half-split pairing; reference gpt.py:116-147) */
+  const float* rope_cos;
+  const float* rope_sin;
+  int seq_len;
+  int rope_cols;
+  /* residual + dropout epilogue (reference gpt.py:240,282,308,314) */
+  const float* residual;
+  float dropout_p;
+  const unsigned long long* rng_state; /* device {seed, offset}; may be NULL when dropout_p == 0 */
+  unsigned int rng_stream;
+  /* SwiGLU epilogues (reference gpt.py:278-281) */
+  void* aux;
+  int ld_aux;
+  int half_n;
+} b200_gemm_args;
+
+/* Reference ops G3/G6/G8/G9 (gpt.py:185-187,239,278-281,447) and their backward GEMMs. */
+int b200_gemm_bf16(const b200_gemm_args* args, void* stream);
+
+/* ---------------------------------------------------------------- normalisation / elementwise */
+/* Token embedding gather into the fp32 residual stream (reference gpt.py:438). ids: int64 [rows]. */
+int b200_embed_fwd(const int64_t* ids, const void* weight_bf16, float* out, int rows, int hidden, int vocab,
+                   void* stream);
+/* Scatter-add of the residual gradient into the (tied) embedding gradient (fp32 [vocab, hidden]). */
+int b200_embed_bwd(const int64_t* ids, const float* dx, float* dweight, int rows, int hidden, int vocab,
+                   void* stream);
+
+/* RMSNorm, one pass: y(bf16) = x * rsqrt(mean(x^2)+eps) * w ; rstd saved (reference gpt.py:66-67). */
+int b200_rmsnorm_fwd(const float* x, const void* w_bf16, void* y_bf16, float* rstd, int rows, int hidden, float eps,
+                     void* stream);
+/* dx (fp32) += d/dx ; dw (fp32 [hidden]) += d/dw (atomics).  dy is bf16. */
+int b200_rmsnorm_bwd(const void* dy_bf16, const float* x, const void* w_bf16, const float* rstd, float* dx_accum,
+                     float* dw_accum, int rows, int hidden, void* stream);
+
+/* out(fp32) = residual + dropout(y bf16)   -- unfused companion of B200_EPI_RESID_DROPOUT */
+int b200_resid_dropout_fwd(const void* y_bf16, const float* residual, float* out, int rows, int cols, float p,
+                           const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+/* dy(bf16) = dropout_mask * dx / (1-p)     -- gradient fed to the o_proj / down_proj backward GEMMs */
+int b200_dropout_bwd_cast(const float* dx, void* dy_bf16, int rows, int cols, float p,
+                          const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+/* keep-mask (uint8) of a [rows, cols] dropout op, for tests / oracles */
+int b200_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned long long* rng_state,
+                      unsigned int rng_stream, void* stream);
+
+/* In-place rotary embedding on the q and k column ranges of a packed [rows, 3h] bf16 tensor.
+ * inverse != 0 applies the transposed rotation (backward).  Unfused companion of B200_EPI_ROPE_BF16. */
+int b200_rope_inplace(void* qkv_bf16, const float* cos, const float* sin, int rows, int ld, int rope_cols,
+                      int seq_len, int inverse, void* stream);
+
+/* SwiGLU: act = silu(g)*u from gu=[g|u] ([rows, 2I]);  backward: dgu from d_act and gu. */
+int b200_swiglu_fwd(const void* gu_bf16, void* act_bf16, int rows, int inter, void* stream);
+int b200_swiglu_bwd(const void* dact_bf16, const void* gu_bf16, void* dgu_bf16, int rows, int inter, void* stream);
+
+/* ---------------------------------------------------------------- attention ----------------- */
+/* Causal flash attention over packed qkv [B*S, 3h] (bf16, q|k|v column blocks, head_dim 64) with
+ * Philox dropout on the probabilities; never materialises [S,S] (reference gpt.py:199-234).
+ * out: [B*S, h] bf16 in [B,S,H,D] order (what o_proj consumes, so the reference's
+ * transpose+contiguous copy at gpt.py:238 disappears); lse: [B, H, S] fp32. */
+int b200_attn_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int seq, int heads, float dropout_p,
+                  const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+/* dqkv: [B*S, 3h] bf16.  delta: caller-provided scratch [B, H, S] fp32; dq_accum: caller-provided fp32
+ * scratch [B*S, h], zeroed by the call. */
+int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                  void* dqkv_bf16, float* delta, float* dq_accum, int batch, int seq, int heads, float dropout_p,
+                  const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+
+/* ---------------------------------------------------------------- LM head loss -------------- */
+/* Fused softmax cross-entropy forward+backward over a chunk of logits (reference gpt.py:449-453).
+ * logits: bf16 [rows, ld] (ld >= vocab, padded columns ignored); labels: int64 [rows], <0 = ignore.
+ * In place: logits <- (softmax - onehot) * grad_scale (0 for ignored rows / padded columns).
+ * loss_sum (fp32 device scalar) += sum over rows of (lse - logit[label]) * loss_scale. */
+int b200_ce_fwd_bwd(void* logits_bf16, const int64_t* labels, float* loss_sum, int rows, int vocab, int ld,
+                    float loss_scale, float grad_scale, void* stream);
+
+/* ---------------------------------------------------------------- optimizer ----------------- */
+/* Fused AdamW over flat element range [lo, hi) (reference ddp_trainer.py:229-234, fsdp_trainer.py:338-343).
+ * master/grad are indexed by the GLOBAL flat offset; exp_avg/exp_avg_sq by (offset - lo).
+ * decay_chunks: uint8 per 128-element chunk (global chunk index).  grad_scale: device fp32 scalar
+ * multiplied into the gradient (clip coefficient).  Writes the bf16 shadow copy when non-NULL. */
+int b200_adamw(float* master, const float* grad, float* exp_avg, float* exp_avg_sq, void* shadow_bf16,
+               const uint8_t* decay_chunks, long long lo, long long hi, int step, float lr, float beta1, float beta2,
+               float eps, float weight_decay, const float* grad_scale, void* stream);
+/* out[0] += sum(x[lo:hi]^2)  (grad-norm partial; reference ddp_trainer.py:350) */
+int b200_sumsq(const float* x, long long lo, long long hi, float* out, void* stream);
+/* scale[0] = pre_scale * min(1, max_norm / (sqrt(sumsq[0]) + 1e-6));  max_norm <= 0 disables clipping */
+int b200_clip_coef(const float* sumsq, float max_norm, float pre_scale, float* scale, float* norm_out, void* stream);
+/* rng_state[1] += delta  (device-side offset bump: keeps dropout fresh under CUDA-graph replay) */
+int b200_rng_advance(unsigned long long* rng_state, unsigned long long delta, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_TRAINER_H_ */
