@@ -1,0 +1,650 @@
+// Causal flash attention forward + backward on tcgen05 (head_dim 64), with Philox dropout on the
+// probabilities.  Replaces the reference's manual O(S^2) path (gpt.py:230-234: QK^T bmm -> triu mask
+// -> fp32 softmax -> dropout -> @V, which materialises [B,H,S,S]) and its SDPA path (gpt.py:199-206).
+//
+// Data layout: packed qkv [B*S, 3h] bf16 straight out of the fused QKV GEMM; one TMA tensor map over
+// it serves Q, K and V tiles (column offsets hd*64, h + hd*64, 2h + hd*64).  Output is written in
+// [B, S, H, D] order, i.e. the [B*S, h] matrix o_proj consumes.
+//
+// Forward CTA = (q block of 128 rows, head, batch), 6 warps:
+//   warp 0     TMA producer: Q once, K/V tiles through 2-stage rings
+//   warp 1     MMA issuer:   S_j = Q K_j^T  (TMEM, double buffered)  and  O_j = P_j V_j (TMEM, double buffered)
+//   warps 2-5  softmax: thread r owns query row r.  tcgen05.ld S row -> online softmax in the exp2
+//              domain -> dropout -> bf16 P tile written to 128B-swizzled smem (A operand of P V) ->
+//              running O kept in registers: o = o * alpha + O_j (no TMEM rescale pass).
+// Backward CTA = (kv block, head, batch) looping over q blocks i >= j; five MMAs per pair:
+//   S = Q K^T, dP = dO V^T, dV += P~^T dO, dK += dS^T Q, dQ_i = dS K  (dQ reduced with red.global.add.f32)
+// P~ / dS tiles are written once to smem and consumed both K-major (dS K) and MN-major (P~^T dO,
+// dS^T Q) through different UMMA descriptors -- no transposes.
+//
+// LSE is stored in the base-2 domain *including* the 1/sqrt(D) scale:  lse2 = max2 + log2(sum).
+#include <cuda_bf16.h>
+#include <math.h>
+
+#include "../include/b200_trainer.h"
+#include "common/host.h"
+#include "common/philox.cuh"
+#include "common/ptx.cuh"
+
+namespace b200 {
+
+constexpr int kBlk = 128;      // q rows per tile == kv rows per tile
+constexpr int kD = 64;         // head_dim
+constexpr int kTile = kBlk * kD * 2;          // 16 KB: [128 rows][128 B]
+constexpr int kPTile = 2 * kTile;             // 32 KB: two 64-column sub-tiles of a 128x128 bf16 matrix
+constexpr float kScale = 0.125f;              // 1/sqrt(64)
+constexpr float kScale2 = 0.125f * 1.4426950408889634f;
+
+struct AttnParams {
+  int B, S, H;
+  int S8;                // ceil(S/8): dropout groups per score row
+  float p_drop;
+  const unsigned long long* rng;
+  unsigned int rng_stream;
+  __nv_bfloat16* out;    // fwd: [B*S, h]
+  float* lse;            // [B, H, S] base-2
+  // backward
+  const float* delta;    // [B, H, S]
+  float* dq_accum;       // [B*S, h] fp32
+  __nv_bfloat16* dqkv;   // [B*S, 3h]
+};
+
+// 16-byte chunk `cc` (0..7) of row `row` inside a [rows][128 B] 128B-swizzled tile
+__device__ __forceinline__ uint32_t swz(uint32_t tile_base, int row, int cc) {
+  return tile_base + row * 128 + ((cc ^ (row & 7)) << 4);
+}
+__device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
+}
+
+// ================================================================================================ forward
+struct FwdSmem {
+  static constexpr int kQ = 0;
+  static constexpr int kK = kQ + kTile;            // 2 stages
+  static constexpr int kV = kK + 2 * kTile;        // 2 stages
+  static constexpr int kP = kV + 2 * kTile;        // 2 buffers x 32 KB
+  static constexpr int kBars = kP + 2 * kPTile;
+  static constexpr int kTotal = kBars + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(192, 1)
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::kBars);
+  uint64_t* q_full = bars;            // 1
+  uint64_t* k_full = bars + 1;        // 2
+  uint64_t* k_empty = bars + 3;       // 2
+  uint64_t* v_full = bars + 5;        // 2
+  uint64_t* v_empty = bars + 7;       // 2
+  uint64_t* s_full = bars + 9;        // 2
+  uint64_t* s_free = bars + 11;       // 2 (count 4)
+  uint64_t* p_ready = bars + 13;      // 2 (count 4)
+  uint64_t* o_full = bars + 15;       // 2
+  uint64_t* o_free = bars + 17;       // 2 (count 4)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 19);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.S + kBlk - 1) / kBlk;
+  const int qi = nq - 1 - blockIdx.x;  // heavy (long) rows first
+  const int hd = blockIdx.y, b = blockIdx.z;
+  const int h = p.H * kD;
+  const int nkv = qi + 1;
+  const int row_base = b * p.S;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    mbar_init(q_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&k_full[i], 1);
+      mbar_init(&k_empty[i], 1);
+      mbar_init(&v_full[i], 1);
+      mbar_init(&v_empty[i], 1);
+      mbar_init(&s_full[i], 1);
+      mbar_init(&s_free[i], 4);
+      mbar_init(&p_ready[i], 4);
+      mbar_init(&o_full[i], 1);
+      mbar_init(&o_free[i], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_ptr;
+  const uint32_t tS[2] = {tmem + 0, tmem + 128};
+  const uint32_t tO[2] = {tmem + 256, tmem + 320};
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(q_full, kTile);
+      tma_load_2d(smem + FwdSmem::kQ, &tm_qkv, q_full, hd * kD, row_base + qi * kBlk);
+      for (int j = 0; j < nkv; ++j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&k_empty[st], ph ^ 1);
+        mbar_expect_tx(&k_full[st], kTile);
+        tma_load_2d(smem + FwdSmem::kK + st * kTile, &tm_qkv, &k_full[st], h + hd * kD, row_base + j * kBlk);
+        mbar_wait(&v_empty[st], ph ^ 1);
+        mbar_expect_tx(&v_full[st], kTile);
+        tma_load_2d(smem + FwdSmem::kV + st * kTile, &tm_qkv, &v_full[st], 2 * h + hd * kD, row_base + j * kBlk);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, false, false);
+      constexpr uint32_t idesc_o = make_idesc_bf16(128, 64, false, true);
+      const uint32_t q_addr = smem_u32(smem + FwdSmem::kQ);
+      mbar_wait(q_full, 0);
+      auto issue_s = [&](int j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&k_full[st], ph);
+        mbar_wait(&s_free[st], ph ^ 1);
+        tc_fence_after();
+        const uint32_t k_addr = smem_u32(smem + FwdSmem::kK + st * kTile);
+#pragma unroll
+        for (int t = 0; t < kD / 16; ++t)
+          umma_bf16_ss(tS[st], make_smem_desc_sw128(q_addr + t * 32, 16, 1024),
+                       make_smem_desc_sw128(k_addr + t * 32, 16, 1024), idesc_s, t > 0);
+        tc_commit(&k_empty[st]);
+        tc_commit(&s_full[st]);
+      };
+      auto issue_pv = [&](int j) {
+        const int st = j & 1;
+        const uint32_t ph = (j >> 1) & 1;
+        mbar_wait(&p_ready[st], ph);
+        mbar_wait(&v_full[st], ph);
+        mbar_wait(&o_free[st], ph ^ 1);
+        tc_fence_after();
+        const uint32_t p_addr = smem_u32(smem + FwdSmem::kP + st * kPTile);
+        const uint32_t v_addr = smem_u32(smem + FwdSmem::kV + st * kTile);
+#pragma unroll
+        for (int t = 0; t < kBlk / 16; ++t)
+          umma_bf16_ss(tO[st], make_smem_desc_sw128(p_addr + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
+                       make_smem_desc_sw128(v_addr + t * 2048, kTile, 1024), idesc_o, t > 0);
+        tc_commit(&v_empty[st]);
+        tc_commit(&o_full[st]);
+      };
+      issue_s(0);
+      for (int j = 0; j < nkv; ++j) {
+        if (j + 1 < nkv) issue_s(j + 1);
+        issue_pv(j);
+      }
+    }
+  } else {
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;                 // row within the q tile
+    const int qrow = qi * kBlk + r;               // position in the sequence
+    const uint32_t lane_off = uint32_t(qd * 32) << 16;
+    const bool drop = p.p_drop > 0.f;
+    const uint32_t thresh = dropout_threshold16(p.p_drop);
+    unsigned long long seed = 0, offs = 0;
+    if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
+    const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
+
+    float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
+    float o[kD];
+#pragma unroll
+    for (int e = 0; e < kD; ++e) o[e] = 0.f;
+
+    for (int j = 0; j < nkv; ++j) {
+      const int st = j & 1;
+      const uint32_t ph = (j >> 1) & 1;
+      const bool diag = (j == qi);
+      mbar_wait(&s_full[st], ph);
+      tc_fence_after();
+      // pass 1: row maximum
+      float mx = m;
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32b_x32(tS[st] + lane_off + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) {
+          const float s = __uint_as_float(v[e]) * kScale2;
+          if (!diag || (c * 32 + e) <= r) mx = fmaxf(mx, s);
+        }
+      }
+      const float m_use = (mx == -INFINITY) ? 0.f : mx;
+      const float alpha = exp2f(m - m_use);
+      l *= alpha;
+      // pass 2: probabilities -> smem (bf16, dropout applied, unnormalised)
+      const uint32_t p_base = smem_u32(smem + FwdSmem::kP + st * kPTile);
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32b_x32(tS[st] + lane_off + c * 32, v);
+        tmem_ld_wait();
+        const uint32_t sub = p_base + (c >> 1) * kTile;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint32_t keep = 0xFF;
+          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + c * 32 + g * 8) >> 3), thresh);
+          float pv[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int col = c * 32 + g * 8 + e;
+            float pe = exp2f(__uint_as_float(v[g * 8 + e]) * kScale2 - m_use);
+            if (diag && col > r) pe = 0.f;
+            l += pe;
+            pv[e] = ((keep >> e) & 1) ? pe : 0.f;
+          }
+          st_shared_v4(swz(sub, r, (c & 1) * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
+                       pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(&p_ready[st]);
+        mbar_arrive(&s_free[st]);
+      }
+      // fold in O_{j-1}
+      if (j > 0) {
+        const int pb = (j - 1) & 1;
+        mbar_wait(&o_full[pb], ((j - 1) >> 1) & 1);
+        tc_fence_after();
+#pragma unroll
+        for (int c = 0; c < 2; ++c) {
+          uint32_t v[32];
+          __syncwarp();
+          tmem_ld_32x32b_x32(tO[pb] + lane_off + c * 32, v);
+          tmem_ld_wait();
+#pragma unroll
+          for (int e = 0; e < 32; ++e) o[c * 32 + e] = o[c * 32 + e] * alpha_prev + __uint_as_float(v[e]);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&o_free[pb]);
+      }
+      alpha_prev = alpha;
+      m = m_use;
+    }
+    {
+      const int pb = (nkv - 1) & 1;
+      mbar_wait(&o_full[pb], ((nkv - 1) >> 1) & 1);
+      tc_fence_after();
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32b_x32(tO[pb] + lane_off + c * 32, v);
+        tmem_ld_wait();
+#pragma unroll
+        for (int e = 0; e < 32; ++e) o[c * 32 + e] = o[c * 32 + e] * alpha_prev + __uint_as_float(v[e]);
+      }
+    }
+    if (qrow < p.S) {
+      const float inv = (drop ? 1.f / (1.f - p.p_drop) : 1.f) / l;
+      __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD;
+#pragma unroll
+      for (int g = 0; g < 8; ++g)
+        *reinterpret_cast<uint4*>(dst + g * 8) =
+            make_uint4(pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv), pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv),
+                       pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv), pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv));
+      p.lse[size_t(b * p.H + hd) * p.S + qrow] = m + log2f(l);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem);
+  }
+}
+
+// ================================================================================================ backward
+// delta[b,h,s] = sum_d dO * O   (one thread per (row, head))
+__global__ void attn_delta_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                  float* __restrict__ delta, int B, int S, int H) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= (long long)B * S * H) return;
+  const int hd = int(t % H);
+  const long long row = t / H;
+  const int b = int(row / S), s = int(row % S);
+  const uint4* po = reinterpret_cast<const uint4*>(o + row * (H * kD) + hd * kD);
+  const uint4* pd = reinterpret_cast<const uint4*>(d_o + row * (H * kD) + hd * kD);
+  float acc = 0.f;
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const uint4 a = po[i], c = pd[i];
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(aw[e]), y = unpack_bf16x2(cw[e]);
+      acc += x.x * y.x + x.y * y.y;
+    }
+  }
+  delta[size_t(b * H + hd) * S + s] = acc;
+}
+
+// dq (fp32 accumulator) -> bf16 q-columns of dqkv
+__global__ void attn_dq_cast_kernel(const float* __restrict__ dq, __nv_bfloat16* __restrict__ dqkv, long long rows,
+                                    int h) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const int gpr = h / 8;
+  if (t >= rows * gpr) return;
+  const long long row = t / gpr;
+  const int c = int(t % gpr) * 8;
+  const float4 a = *reinterpret_cast<const float4*>(dq + row * h + c), bq = *reinterpret_cast<const float4*>(dq + row * h + c + 4);
+  *reinterpret_cast<uint4*>(dqkv + row * 3 * h + c) =
+      make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(bq.x, bq.y), pack_bf16x2(bq.z, bq.w));
+}
+
+struct BwdSmem {
+  static constexpr int kK = 0;
+  static constexpr int kV = kK + kTile;
+  static constexpr int kQ = kV + kTile;            // 2 stages
+  static constexpr int kdO = kQ + 2 * kTile;       // 2 stages
+  static constexpr int kP = kdO + 2 * kTile;       // 32 KB
+  static constexpr int kdS = kP + kPTile;          // 32 KB
+  static constexpr int kBars = kdS + kPTile;
+  static constexpr int kTotal = kBars + 256 + 1024;
+};
+
+__global__ void __launch_bounds__(192, 1)
+attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
+                const AttnParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::kBars);
+  uint64_t* kv_full = bars;            // 1
+  uint64_t* qdo_full = bars + 1;       // 2
+  uint64_t* qdo_empty = bars + 3;      // 2
+  uint64_t* sdp_full = bars + 5;       // 1
+  uint64_t* s_free = bars + 6;         // 1 (count 4)
+  uint64_t* pds_ready = bars + 7;      // 1 (count 4)
+  uint64_t* dq_full = bars + 8;        // 1
+  uint64_t* dq_free = bars + 9;        // 1 (count 4)
+  uint64_t* acc_full = bars + 10;      // 1
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 11);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int nq = (p.S + kBlk - 1) / kBlk;
+  const int j = blockIdx.x;  // kv block (small j = most q blocks = heaviest, scheduled first)
+  const int hd = blockIdx.y, b = blockIdx.z;
+  const int h = p.H * kD;
+  const int niter = nq - j;
+  const int row_base = b * p.S;
+
+  if (threadIdx.x == 0) {
+    tma_prefetch_desc(&tm_qkv);
+    tma_prefetch_desc(&tm_do);
+    mbar_init(kv_full, 1);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&qdo_full[i], 1);
+      mbar_init(&qdo_empty[i], 1);
+    }
+    mbar_init(sdp_full, 1);
+    mbar_init(s_free, 4);
+    mbar_init(pds_ready, 4);
+    mbar_init(dq_full, 1);
+    mbar_init(dq_free, 4);
+    mbar_init(acc_full, 1);
+    fence_barrier_init();
+  }
+  if (warp == 1) tmem_alloc<512>(tmem_ptr);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_ptr;
+  const uint32_t tS = tmem, tdP = tmem + 128, tdV = tmem + 256, tdK = tmem + 320, tdQ = tmem + 384;
+
+  if (warp == 0) {
+    if (lane == 0) {
+      mbar_expect_tx(kv_full, 2 * kTile);
+      tma_load_2d(smem + BwdSmem::kK, &tm_qkv, kv_full, h + hd * kD, row_base + j * kBlk);
+      tma_load_2d(smem + BwdSmem::kV, &tm_qkv, kv_full, 2 * h + hd * kD, row_base + j * kBlk);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        mbar_wait(&qdo_empty[st], ph ^ 1);
+        mbar_expect_tx(&qdo_full[st], 2 * kTile);
+        tma_load_2d(smem + BwdSmem::kQ + st * kTile, &tm_qkv, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
+        tma_load_2d(smem + BwdSmem::kdO + st * kTile, &tm_do, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
+      }
+    }
+  } else if (warp == 1) {
+    if (lane == 0) {
+      constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, false, false);    // Q K^T, dO V^T
+      constexpr uint32_t idesc_tt = make_idesc_bf16(128, 64, true, true);      // P^T dO, dS^T Q
+      constexpr uint32_t idesc_dq = make_idesc_bf16(128, 64, false, true);     // dS K
+      const uint32_t k_addr = smem_u32(smem + BwdSmem::kK), v_addr = smem_u32(smem + BwdSmem::kV);
+      const uint32_t p_addr = smem_u32(smem + BwdSmem::kP), ds_addr = smem_u32(smem + BwdSmem::kdS);
+      mbar_wait(kv_full, 0);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;
+        const uint32_t ph = (it >> 1) & 1;
+        const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
+        const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
+        mbar_wait(&qdo_full[st], ph);
+        mbar_wait(s_free, (it & 1) ^ 1);
+        tc_fence_after();
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          umma_bf16_ss(tS, make_smem_desc_sw128(q_addr + t * 32, 16, 1024), make_smem_desc_sw128(k_addr + t * 32, 16, 1024),
+                       idesc_s, t > 0);
+#pragma unroll
+        for (int t = 0; t < 4; ++t)
+          umma_bf16_ss(tdP, make_smem_desc_sw128(do_addr + t * 32, 16, 1024), make_smem_desc_sw128(v_addr + t * 32, 16, 1024),
+                       idesc_s, t > 0);
+        tc_commit(sdp_full);
+        mbar_wait(pds_ready, it & 1);
+        mbar_wait(dq_free, (it & 1) ^ 1);
+        tc_fence_after();
+#pragma unroll
+        for (int t = 0; t < 8; ++t)  // dV += P~^T dO   (K = 128 q rows, 16 per step)
+          umma_bf16_ss(tdV, make_smem_desc_sw128(p_addr + t * 2048, kTile, 1024),
+                       make_smem_desc_sw128(do_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
+#pragma unroll
+        for (int t = 0; t < 8; ++t)  // dK += dS^T Q
+          umma_bf16_ss(tdK, make_smem_desc_sw128(ds_addr + t * 2048, kTile, 1024),
+                       make_smem_desc_sw128(q_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
+#pragma unroll
+        for (int t = 0; t < 8; ++t)  // dQ_i = dS K     (K = 128 kv, 16 per step)
+          umma_bf16_ss(tdQ, make_smem_desc_sw128(ds_addr + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
+                       make_smem_desc_sw128(k_addr + t * 2048, kTile, 1024), idesc_dq, t > 0);
+        tc_commit(&qdo_empty[st]);
+        tc_commit(dq_full);
+      }
+      tc_commit(acc_full);
+    }
+  } else {
+    const int qd = warp & 3;
+    const int r = qd * 32 + lane;
+    const uint32_t lane_off = uint32_t(qd * 32) << 16;
+    const bool drop = p.p_drop > 0.f;
+    const uint32_t thresh = dropout_threshold16(p.p_drop);
+    const float inv_keep = drop ? 1.f / (1.f - p.p_drop) : 1.f;
+    unsigned long long seed = 0, offs = 0;
+    if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
+    const uint32_t p_base = smem_u32(smem + BwdSmem::kP), ds_base = smem_u32(smem + BwdSmem::kdS);
+
+    auto drain_dq = [&](int it) {
+      const int qrow = (j + it) * kBlk + r;
+      mbar_wait(dq_full, it & 1);
+      tc_fence_after();
+      float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD;
+#pragma unroll
+      for (int c = 0; c < 2; ++c) {
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32b_x32(tdQ + lane_off + c * 32, v);
+        tmem_ld_wait();
+        if (qrow < p.S) {
+#pragma unroll
+          for (int g = 0; g < 8; ++g)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c * 32 + g * 4),
+                         "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
+                         "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
+                         : "memory");
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(dq_free);
+    };
+
+    for (int it = 0; it < niter; ++it) {
+      if (it > 0) drain_dq(it - 1);
+      const int i = j + it;
+      const int qrow = i * kBlk + r;
+      const bool diag = (i == j);
+      const bool row_ok = qrow < p.S;
+      const size_t stat = size_t(b * p.H + hd) * p.S + (row_ok ? qrow : 0);
+      const float lse2 = row_ok ? p.lse[stat] : INFINITY;
+      const float dl = row_ok ? p.delta[stat] : 0.f;
+      const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
+      mbar_wait(sdp_full, it & 1);
+      tc_fence_after();
+#pragma unroll 1
+      for (int c = 0; c < 4; ++c) {
+        uint32_t sv[32], dv[32];
+        __syncwarp();
+        tmem_ld_32x32b_x32(tS + lane_off + c * 32, sv);
+        tmem_ld_32x32b_x32(tdP + lane_off + c * 32, dv);
+        tmem_ld_wait();
+        const int sub = (c >> 1) * kTile;
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          uint32_t keep = 0xFF;
+          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + c * 32 + g * 8) >> 3), thresh);
+          float pd[8], ds[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            const int col = c * 32 + g * 8 + e;
+            float pe = exp2f(__uint_as_float(sv[g * 8 + e]) * kScale2 - lse2);
+            if (diag && col > r) pe = 0.f;
+            const bool k1 = (keep >> e) & 1;
+            const float dpe = k1 ? __uint_as_float(dv[g * 8 + e]) * inv_keep : 0.f;
+            ds[e] = pe * (dpe - dl) * kScale;
+            pd[e] = k1 ? pe * inv_keep : 0.f;
+          }
+          const int cc = (c & 1) * 4 + g;
+          st_shared_v4(swz(p_base + sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
+                       pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
+          st_shared_v4(swz(ds_base + sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                       pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+        }
+      }
+      tc_fence_before();
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        mbar_arrive(pds_ready);
+        mbar_arrive(s_free);
+      }
+    }
+    drain_dq(niter - 1);
+
+    // dK / dV of this kv block: thread r owns kv row r
+    mbar_wait(acc_full, 0);
+    tc_fence_after();
+    const int kvrow = j * kBlk + r;
+    __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD;
+    __nv_bfloat16* dv_dst = dk_dst + h;
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      uint32_t kv_[32], vv_[32];
+      __syncwarp();
+      tmem_ld_32x32b_x32(tdK + lane_off + c * 32, kv_);
+      tmem_ld_32x32b_x32(tdV + lane_off + c * 32, vv_);
+      tmem_ld_wait();
+      if (kvrow < p.S) {
+#pragma unroll
+        for (int g = 0; g < 4; ++g) {
+          *reinterpret_cast<uint4*>(dk_dst + c * 32 + g * 8) = make_uint4(
+              pack_bf16x2(__uint_as_float(kv_[g * 8 + 0]), __uint_as_float(kv_[g * 8 + 1])),
+              pack_bf16x2(__uint_as_float(kv_[g * 8 + 2]), __uint_as_float(kv_[g * 8 + 3])),
+              pack_bf16x2(__uint_as_float(kv_[g * 8 + 4]), __uint_as_float(kv_[g * 8 + 5])),
+              pack_bf16x2(__uint_as_float(kv_[g * 8 + 6]), __uint_as_float(kv_[g * 8 + 7])));
+          *reinterpret_cast<uint4*>(dv_dst + c * 32 + g * 8) = make_uint4(
+              pack_bf16x2(__uint_as_float(vv_[g * 8 + 0]), __uint_as_float(vv_[g * 8 + 1])),
+              pack_bf16x2(__uint_as_float(vv_[g * 8 + 2]), __uint_as_float(vv_[g * 8 + 3])),
+              pack_bf16x2(__uint_as_float(vv_[g * 8 + 4]), __uint_as_float(vv_[g * 8 + 5])),
+              pack_bf16x2(__uint_as_float(vv_[g * 8 + 6]), __uint_as_float(vv_[g * 8 + 7])));
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc<512>(tmem);
+  }
+}
+
+}  // namespace b200
+
+using namespace b200;
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, int heads, float dropout_p,
+                  const unsigned long long* rng, unsigned int rng_stream, void* stream) {
+  B200_REQUIRE(batch > 0 && seq > 0 && heads > 0, "attn_fwd: empty problem");
+  B200_REQUIRE(dropout_p == 0.f || rng != nullptr, "attn_fwd: rng_state required when dropout_p > 0");
+  const int h = heads * kD;
+  CUtensorMap tm;
+  int rc = make_tmap_2d_bf16(&tm, qkv, 3 * (uint64_t)h, (uint64_t)batch * seq, 3 * (uint64_t)h, 64, kBlk);
+  if (rc) return rc;
+  AttnParams p{};
+  p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
+  p.out = (__nv_bfloat16*)out; p.lse = lse;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::kTotal));
+    configured = true;
+  }
+  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  attn_fwd_kernel<<<grid, 192, FwdSmem::kTotal, STREAM(stream)>>>(tm, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta,
+                  float* dq_accum, int batch, int seq, int heads, float dropout_p, const unsigned long long* rng,
+                  unsigned int rng_stream, void* stream) {
+  B200_REQUIRE(batch > 0 && seq > 0 && heads > 0, "attn_bwd: empty problem");
+  B200_REQUIRE(dropout_p == 0.f || rng != nullptr, "attn_bwd: rng_state required when dropout_p > 0");
+  const int h = heads * kD;
+  const long long rows = (long long)batch * seq;
+  CUtensorMap tm_qkv, tm_do;
+  int rc = make_tmap_2d_bf16(&tm_qkv, qkv, 3 * (uint64_t)h, (uint64_t)rows, 3 * (uint64_t)h, 64, kBlk);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tm_do, dout, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 64, kBlk);
+  if (rc) return rc;
+  cudaStream_t s = STREAM(stream);
+  const long long nd = rows * heads;
+  attn_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
+                                                                 delta, batch, seq, heads);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_CHECK_CUDA(cudaMemsetAsync(dq_accum, 0, size_t(rows) * h * sizeof(float), s));
+  AttnParams p{};
+  p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
+  p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
+  static bool configured = false;
+  if (!configured) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal));
+    configured = true;
+  }
+  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  attn_bwd_kernel<<<grid, 192, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  const long long ng = rows * (h / 8);
+  attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -1,0 +1,60 @@
+"""tcgen05 flash attention fwd/bwd vs the fp32 manual attention of reference gpt.py:230-234
+(same dropout keep-mask, regenerated from the kernel's Philox stream)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _attn_mask(B, H, S, p, rng, stream):
+    """keep-mask [B,H,S,S] exactly as the attention kernels draw it (groups of 8 along kv)."""
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    S8 = (S + 7) // 8
+    m = torch.zeros(B * H * S, S8 * 8, dtype=torch.uint8, device="cuda")
+    k.dropout_mask(m, p, rng, stream)
+    return m[:, :S].reshape(B, H, S, S).float()
+
+
+@pytest.mark.parametrize("B,S,H,p", [(2, 128, 2, 0.0), (1, 512, 3, 0.0), (2, 384, 2, 0.1), (1, 200, 2, 0.1),
+                                     (2, 1024, 4, 0.1)])
+def test_attention_fwd_bwd(B, S, H, p):
+    from distributed_llm_trainer_b200.ops import kernels as k
+    from distributed_llm_trainer_b200.ops import reference as R
+
+    torch.manual_seed(0)
+    h = H * 64
+    qkv = (torch.randn(B * S, 3 * h, device="cuda") * 0.8).to(torch.bfloat16)
+    rng = torch.tensor([42, 3], dtype=torch.int64, device="cuda")
+    out = torch.zeros(B * S, h, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(B, H, S, device="cuda")
+    k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9)
+    torch.cuda.synchronize()
+
+    def split(t):
+        return t.float().reshape(B, S, 3, H, 64).permute(2, 0, 3, 1, 4)  # [3,B,H,S,D]
+
+    q, kk, v = [x.clone().requires_grad_(True) for x in split(qkv)]
+    mask = _attn_mask(B, H, S, p, rng, 9) if p > 0 else None
+    ref = R.causal_attention(q, kk, v, mask, p)                     # [B,H,S,D]
+    ref_out = ref.permute(0, 2, 1, 3).reshape(B * S, h)
+    err = (out.float() - ref_out).abs().max().item()
+    assert err < 0.03, f"fwd err {err}"
+    # lse (base 2, scaled) against the oracle
+    sc = (q @ kk.transpose(-2, -1)) * 0.125
+    sc = sc.masked_fill(torch.ones(S, S, dtype=torch.bool, device="cuda").triu(1), float("-inf"))
+    ref_lse2 = torch.logsumexp(sc, dim=-1) * 1.4426950408889634
+    assert (lse - ref_lse2).abs().max().item() < 0.02
+
+    dout = (torch.randn(B * S, h, device="cuda") * 0.5).to(torch.bfloat16)
+    ref_out.backward(dout.float())
+    dqkv = torch.zeros(B * S, 3 * h, device="cuda", dtype=torch.bfloat16)
+    delta = torch.zeros(B, H, S, device="cuda")
+    dq_acc = torch.empty(B * S, h, device="cuda")
+    k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 9)
+    torch.cuda.synchronize()
+    got = split(dqkv)
+    for name, g, r_ in (("dq", got[0], q.grad), ("dk", got[1], kk.grad), ("dv", got[2], v.grad)):
+        e = (g - r_).abs().max().item()
+        scale = max(1.0, r_.abs().max().item())
+        assert e < 0.04 * scale, f"{name} err {e} (scale {scale})"
