@@ -1,0 +1,383 @@
+// NVLink 5 / NVSwitch communication kernels over peer-mapped memory (CUDA IPC or symmetric memory):
+// no NCCL on these paths.  Every rank passes a device table of N peer pointers per symmetric buffer.
+//
+//   b200_comm_barrier        signal-pad barrier: st.release.sys of an epoch into every peer's pad, then
+//                            ld.acquire.sys spin on the own pad (bounded: a dead peer traps, never hangs)
+//   b200_reduce_scatter_f32  this rank's slice of the gradient = sum over peers (P2P loads straight from
+//                            the peers' flat fp32 gradient buffers), scaled, written locally, with the
+//                            squared-norm partial folded in         (reference K4/K9 + G13)
+//   b200_adamw_bcast         AdamW on the owned slice (clip coefficient from device memory) whose bf16
+//                            result is stored into EVERY rank's shadow buffer: the all-gather half of the
+//                            all-reduce carries updated parameters (2 B/param) instead of gradients
+//                            (4 B/param) and the optimizer runs on 1/N of the data  (reference K4 + G14)
+//   b200_allreduce_scalars   tiny all-reduce of a few floats through the signal pads (norm^2, loss)
+//   b200_all_gather_bf16     FSDP parameter all-gather by P2P pull               (reference K7/K8)
+//   b200_reduce_scatter_bf16out  FSDP gradient reduce-scatter                    (reference K9)
+//
+// Reference call sites being replaced: torch DDP's bucketed NCCL all-reduce (ddp_trainer.py:167-172,
+// :342), FSDP1's all_gather_into_tensor / reduce_scatter_tensor (fsdp_trainer.py:379-383),
+// clip_grad_norm_ (ddp_trainer.py:350, fsdp_trainer.py:388) and the optimizer steps (:356, :391).
+#include <cuda_bf16.h>
+#include <math.h>
+
+#include "../include/b200_trainer.h"
+#include "common/host.h"
+#include "common/ptx.cuh"
+
+namespace b200 {
+
+constexpr int kMaxRanks = 16;
+constexpr unsigned long long kCommTimeoutNs = 20000000000ull;  // 20 s
+
+struct PeerTable {
+  void* p[kMaxRanks];
+};
+
+__device__ __forceinline__ void st_release_sys_u32(uint32_t* addr, uint32_t v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(addr), "r"(v) : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_sys_u32(const uint32_t* addr) {
+  uint32_t v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_peer_f4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.relaxed.sys.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ uint4 ld_peer_u4(const void* p) {
+  uint4 v;
+  asm volatile("ld.global.relaxed.sys.v4.u32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "l"(p));
+  return v;
+}
+
+// pads.p[r] -> uint32 slots[kMaxRanks * kPadRows] on rank r.  Row `row` keeps barrier epochs separate
+// from scalar-exchange traffic.
+__device__ __forceinline__ void pad_barrier(const PeerTable& pads, int rank, int world, uint32_t epoch, int row) {
+  const int t = threadIdx.x;
+  if (t < world) {
+    __threadfence_system();
+    st_release_sys_u32(reinterpret_cast<uint32_t*>(pads.p[t]) + row * kMaxRanks + rank, epoch);
+    const uint32_t* mine = reinterpret_cast<const uint32_t*>(pads.p[rank]) + row * kMaxRanks + t;
+    const unsigned long long t0 = global_timer_ns();
+    uint32_t spins = 0;
+    // epochs are monotonic; signed distance handles wrap-around
+    while (int32_t(ld_acquire_sys_u32(mine) - epoch) < 0) {
+      if ((++spins & 0xFF) == 0 && global_timer_ns() - t0 > kCommTimeoutNs) {
+        printf("b200: comm barrier timed out waiting for rank %d (rank %d, epoch %u)\n", t, rank, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void comm_barrier_kernel(PeerTable pads, int rank, int world, uint32_t epoch) {
+  pad_barrier(pads, rank, world, epoch, 0);
+}
+
+// dst[i] = scale * sum_r src_r[lo + i]  for i in the owned slice; sumsq += sum(dst^2).
+// `srcs` are the peers' flat gradient buffers (same global indexing); dst is this rank's own buffer.
+template <int kWorld>
+__global__ void __launch_bounds__(512)
+reduce_scatter_f32_kernel(PeerTable srcs, float* __restrict__ dst, long long lo, long long n4, float scale,
+                          float* __restrict__ sumsq, int rank) {
+  float acc = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 v[kWorld];
+#pragma unroll
+    for (int r = 0; r < kWorld; ++r) {
+      const int src = (rank + r) % kWorld;  // rotate so the peers are not all hammering rank 0 first
+      v[r] = ld_peer_f4(reinterpret_cast<const float*>(srcs.p[src]) + lo + 4 * i);
+    }
+    float4 s = v[0];
+#pragma unroll
+    for (int r = 1; r < kWorld; ++r) {
+      s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
+    }
+    s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
+    *reinterpret_cast<float4*>(dst + lo + 4 * i) = s;
+    acc += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
+  }
+  if (sumsq != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ float sh[16];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < (blockDim.x >> 5); ++i) t += sh[i];
+      atomicAdd(sumsq, t);
+    }
+  }
+}
+
+// Generic-world fallback (runtime loop)
+__global__ void __launch_bounds__(512)
+reduce_scatter_f32_generic(PeerTable srcs, float* __restrict__ dst, long long lo, long long n4, float scale,
+                           float* __restrict__ sumsq, int rank, int world) {
+  float acc = 0.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int r = 0; r < world; ++r) {
+      const float4 v = ld_peer_f4(reinterpret_cast<const float*>(srcs.p[(rank + r) % world]) + lo + 4 * i);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    s.x *= scale; s.y *= scale; s.z *= scale; s.w *= scale;
+    *reinterpret_cast<float4*>(dst + lo + 4 * i) = s;
+    acc += s.x * s.x + s.y * s.y + s.z * s.z + s.w * s.w;
+  }
+  if (sumsq != nullptr) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    __shared__ float sh[16];
+    if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      float t = 0.f;
+      for (int i = 0; i < (blockDim.x >> 5); ++i) t += sh[i];
+      atomicAdd(sumsq, t);
+    }
+  }
+}
+
+// AdamW on [lo, lo + 4*n4) of the flat space; bf16 result stored to every peer's shadow buffer.
+__global__ void __launch_bounds__(256)
+adamw_bcast_kernel(float* __restrict__ master, const float* __restrict__ grad, float* __restrict__ m,
+                   float* __restrict__ v, PeerTable shadows, int world, int rank,
+                   const uint8_t* __restrict__ decay_chunks, long long lo, long long n4, float lr, float beta1,
+                   float beta2, float eps, float wd, float step_size, float inv_sqrt_bc2,
+                   const float* __restrict__ grad_scale) {
+  const float gs = grad_scale ? *grad_scale : 1.f;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    const long long gi = lo + 4 * i;
+    float4 p = *reinterpret_cast<const float4*>(master + gi);
+    const float4 g = *reinterpret_cast<const float4*>(grad + gi);
+    float4 mm = reinterpret_cast<const float4*>(m)[i];
+    float4 vv = reinterpret_cast<const float4*>(v)[i];
+    const float decay = decay_chunks[gi >> 7] ? 1.f - lr * wd : 1.f;
+    float* pp = reinterpret_cast<float*>(&p);
+    const float* gg = reinterpret_cast<const float*>(&g);
+    float* pm = reinterpret_cast<float*>(&mm);
+    float* pv = reinterpret_cast<float*>(&vv);
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float ge = gg[e] * gs;
+      pm[e] = beta1 * pm[e] + (1.f - beta1) * ge;
+      pv[e] = beta2 * pv[e] + (1.f - beta2) * ge * ge;
+      pp[e] = pp[e] * decay - step_size * (pm[e] / (sqrtf(pv[e]) * inv_sqrt_bc2 + eps));
+    }
+    *reinterpret_cast<float4*>(master + gi) = p;
+    reinterpret_cast<float4*>(m)[i] = mm;
+    reinterpret_cast<float4*>(v)[i] = vv;
+    const uint2 s = make_uint2(pack_bf16x2(pp[0], pp[1]), pack_bf16x2(pp[2], pp[3]));
+    for (int r = 0; r < world; ++r) {
+      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(shadows.p[(rank + r) % world]) + gi;
+      *reinterpret_cast<uint2*>(dst) = s;
+    }
+  }
+}
+
+// Each rank contributes `n` floats; result (sum over ranks, identical order on every rank) in out[].
+// Exchange area: row 1.. of the signal pads, float slots [rank][n] (n <= 8).
+__global__ void allreduce_scalars_kernel(PeerTable pads, PeerTable xchg, int rank, int world, uint32_t epoch,
+                                         const float* __restrict__ in, float* __restrict__ out, int n) {
+  const int t = threadIdx.x;
+  // xchg.p[r] -> float area [2][kMaxRanks][8] on rank r, double buffered by epoch parity so a fast
+  // rank's next exchange cannot overwrite values a slow rank is still summing
+  const int par = (epoch & 1) * kMaxRanks * 8;
+  if (t < world) {
+    float* dst = reinterpret_cast<float*>(xchg.p[t]) + par + rank * 8;
+    for (int i = 0; i < n; ++i) dst[i] = in[i];
+  }
+  __syncthreads();
+  pad_barrier(pads, rank, world, epoch, 0);
+  if (t < n) {
+    const float* mine = reinterpret_cast<const float*>(xchg.p[rank]) + par;
+    float s = 0.f;
+    for (int r = 0; r < world; ++r) s += *reinterpret_cast<const volatile float*>(mine + r * 8 + t);
+    out[t] = s;
+  }
+}
+
+// dst[r * shard + i] = src_r[i]   (pull every peer's shard into the local full buffer), 16 B units
+__global__ void __launch_bounds__(512)
+all_gather_pull_kernel(PeerTable srcs, uint4* __restrict__ dst, long long shard16, int rank, int world) {
+  const long long total = shard16 * world;
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
+    const int rr = int(i / shard16);
+    const int r = (rank + rr) % world;
+    const long long off = i - rr * shard16;
+    dst[r * shard16 + off] = ld_peer_u4(reinterpret_cast<const uint4*>(srcs.p[r]) + off);
+  }
+}
+
+// FSDP gradient reduce-scatter: peers hold full-unit bf16 gradients; this rank sums its shard in fp32
+// and ACCUMULATES into its fp32 sharded gradient (gradient accumulation across micro-steps).
+__global__ void __launch_bounds__(512)
+reduce_scatter_bf16_accum_kernel(PeerTable srcs, float* __restrict__ dst, long long src_off8, long long n8, float scale,
+                                 int rank, int world) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n8; i += (long long)gridDim.x * blockDim.x) {
+    float acc[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+    for (int r = 0; r < world; ++r) {
+      const uint4 q = ld_peer_u4(reinterpret_cast<const uint4*>(srcs.p[(rank + r) % world]) + src_off8 + i);
+      const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = unpack_bf16x2(w[e]);
+        acc[2 * e] += f.x;
+        acc[2 * e + 1] += f.y;
+      }
+    }
+    float4* d = reinterpret_cast<float4*>(dst + 8 * i);
+    float4 a = d[0], b = d[1];
+    a.x += acc[0] * scale; a.y += acc[1] * scale; a.z += acc[2] * scale; a.w += acc[3] * scale;
+    b.x += acc[4] * scale; b.y += acc[5] * scale; b.z += acc[6] * scale; b.w += acc[7] * scale;
+    d[0] = a;
+    d[1] = b;
+  }
+}
+
+// FSDP gradient reduce-scatter, fp32 wire: peers hold full-unit fp32 gradient staging buffers; this rank
+// sums elements [src_off, src_off + 4*n4) of every peer and ACCUMULATES into its sharded gradient.
+__global__ void __launch_bounds__(512)
+reduce_scatter_f32_accum_kernel(PeerTable srcs, float* __restrict__ dst, long long src_off, long long n4, float scale,
+                                int rank, int world) {
+  for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < n4; i += (long long)gridDim.x * blockDim.x) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 4
+    for (int r = 0; r < world; ++r) {
+      const float4 v = ld_peer_f4(reinterpret_cast<const float*>(srcs.p[(rank + r) % world]) + src_off + 4 * i);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    float4 d = reinterpret_cast<float4*>(dst)[i];
+    d.x += s.x * scale; d.y += s.y * scale; d.z += s.z * scale; d.w += s.w * scale;
+    reinterpret_cast<float4*>(dst)[i] = d;
+  }
+}
+
+static int fill_table(PeerTable* t, const void* const* host_ptrs, int world) {
+  B200_REQUIRE(world >= 1 && world <= kMaxRanks, "comm: world size %d out of range (max %d)", world, kMaxRanks);
+  for (int i = 0; i < kMaxRanks; ++i) t->p[i] = i < world ? const_cast<void*>(host_ptrs[i]) : nullptr;
+  return 0;
+}
+
+}  // namespace b200
+
+using namespace b200;
+#define STREAM(s) reinterpret_cast<cudaStream_t>(s)
+
+extern "C" {
+
+int b200_comm_pad_bytes(void) { return kMaxRanks * 4 * 4 + 2 * kMaxRanks * 8 * 4; }
+
+int b200_comm_barrier(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, void* stream) {
+  PeerTable pads;
+  if (int rc = fill_table(&pads, pad_ptrs, world)) return rc;
+  comm_barrier_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, rank, world, epoch);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_reduce_scatter_f32(const void* const* grad_ptrs, float* dst, long long lo, long long hi, float scale,
+                            float* sumsq, int rank, int world, int max_ctas, void* stream) {
+  B200_REQUIRE(lo % 4 == 0 && hi % 4 == 0 && hi >= lo, "reduce_scatter: range must be 4-element aligned");
+  if (hi == lo) return 0;
+  PeerTable srcs;
+  if (int rc = fill_table(&srcs, grad_ptrs, world)) return rc;
+  const long long n4 = (hi - lo) / 4;
+  long long blocks = (n4 + 511) / 512;
+  const long long cap = max_ctas > 0 ? max_ctas : (long long)sm_count() * 2;
+  if (blocks > cap) blocks = cap;
+  cudaStream_t s = STREAM(stream);
+  switch (world) {
+    case 2: reduce_scatter_f32_kernel<2><<<(unsigned)blocks, 512, 0, s>>>(srcs, dst, lo, n4, scale, sumsq, rank); break;
+    case 4: reduce_scatter_f32_kernel<4><<<(unsigned)blocks, 512, 0, s>>>(srcs, dst, lo, n4, scale, sumsq, rank); break;
+    case 8: reduce_scatter_f32_kernel<8><<<(unsigned)blocks, 512, 0, s>>>(srcs, dst, lo, n4, scale, sumsq, rank); break;
+    default: reduce_scatter_f32_generic<<<(unsigned)blocks, 512, 0, s>>>(srcs, dst, lo, n4, scale, sumsq, rank, world);
+  }
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_adamw_bcast(float* master, const float* grad, float* exp_avg, float* exp_avg_sq,
+                     const void* const* shadow_ptrs, int rank, int world, const uint8_t* decay_chunks, long long lo,
+                     long long hi, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                     const float* grad_scale, int max_ctas, void* stream) {
+  B200_REQUIRE(lo % 4 == 0 && hi % 4 == 0 && hi >= lo, "adamw_bcast: range must be 4-element aligned");
+  if (hi == lo) return 0;
+  PeerTable sh;
+  if (int rc = fill_table(&sh, shadow_ptrs, world)) return rc;
+  const long long n4 = (hi - lo) / 4;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  long long blocks = (n4 + 255) / 256;
+  const long long cap = max_ctas > 0 ? max_ctas : (long long)sm_count() * 8;
+  if (blocks > cap) blocks = cap;
+  adamw_bcast_kernel<<<(unsigned)blocks, 256, 0, STREAM(stream)>>>(
+      master, grad, exp_avg, exp_avg_sq, sh, world, rank, decay_chunks, lo, n4, lr, beta1, beta2, eps, weight_decay,
+      (float)(lr / bc1), (float)(1.0 / sqrt(bc2)), grad_scale);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, const float* in,
+                           float* out, int n, void* stream) {
+  B200_REQUIRE(n >= 1 && n <= 8, "allreduce_scalars: n must be in [1,8]");
+  PeerTable pads, xchg;
+  if (int rc = fill_table(&pads, pad_ptrs, world)) return rc;
+  for (int i = 0; i < kMaxRanks; ++i)
+    xchg.p[i] = pads.p[i] ? reinterpret_cast<char*>(pads.p[i]) + kMaxRanks * 4 * 4 : nullptr;
+  allreduce_scalars_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, xchg, rank, world, epoch, in, out, n);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_all_gather_bf16(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
+                         int max_ctas, void* stream) {
+  B200_REQUIRE(shard_elems % 8 == 0, "all_gather: shard must be a multiple of 8 bf16 elements");
+  PeerTable srcs;
+  if (int rc = fill_table(&srcs, shard_ptrs, world)) return rc;
+  const long long shard16 = shard_elems / 8;
+  long long blocks = (shard16 * world + 511) / 512;
+  const long long cap = max_ctas > 0 ? max_ctas : (long long)sm_count() * 2;
+  if (blocks > cap) blocks = cap;
+  if (blocks < 1) blocks = 1;
+  all_gather_pull_kernel<<<(unsigned)blocks, 512, 0, STREAM(stream)>>>(srcs, (uint4*)dst, shard16, rank, world);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_reduce_scatter_f32_accum(const void* const* full_grad_ptrs, float* dst_shard, long long src_offset,
+                                  long long n, float scale, int rank, int world, int max_ctas, void* stream) {
+  B200_REQUIRE(src_offset % 4 == 0 && n % 4 == 0, "reduce_scatter_f32_accum: offset/size must be multiples of 4");
+  if (n == 0) return 0;
+  PeerTable srcs;
+  if (int rc = fill_table(&srcs, full_grad_ptrs, world)) return rc;
+  long long blocks = (n / 4 + 511) / 512;
+  const long long cap = max_ctas > 0 ? max_ctas : (long long)sm_count() * 2;
+  if (blocks > cap) blocks = cap;
+  reduce_scatter_f32_accum_kernel<<<(unsigned)blocks, 512, 0, STREAM(stream)>>>(srcs, dst_shard, src_offset, n / 4,
+                                                                                 scale, rank, world);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_reduce_scatter_bf16_accum(const void* const* full_grad_ptrs, float* dst_shard, long long src_offset,
+                                   long long n, float scale, int rank, int world, int max_ctas, void* stream) {
+  B200_REQUIRE(src_offset % 8 == 0 && n % 8 == 0, "reduce_scatter_bf16: offset/size must be multiples of 8");
+  if (n == 0) return 0;
+  PeerTable srcs;
+  if (int rc = fill_table(&srcs, full_grad_ptrs, world)) return rc;
+  long long blocks = (n / 8 + 511) / 512;
+  const long long cap = max_ctas > 0 ? max_ctas : (long long)sm_count() * 2;
+  if (blocks > cap) blocks = cap;
+  reduce_scatter_bf16_accum_kernel<<<(unsigned)blocks, 512, 0, STREAM(stream)>>>(srcs, dst_shard, src_offset / 8, n / 8,
+                                                                                  scale, rank, world);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"

@@ -52,6 +52,13 @@ _SIGS = {
     "b200_sumsq": [_P, _LL, _LL, _P, _P],
     "b200_clip_coef": [_P, _F, _F, _P, _P, _P],
     "b200_rng_advance": [_P, C.c_ulonglong, _P],
+    "b200_comm_barrier": [_P, _I, _I, _U, _P],
+    "b200_reduce_scatter_f32": [_P, _P, _LL, _LL, _F, _P, _I, _I, _I, _P],
+    "b200_adamw_bcast": [_P, _P, _P, _P, _P, _I, _I, _P, _LL, _LL, _I, _F, _F, _F, _F, _F, _P, _I, _P],
+    "b200_allreduce_scalars": [_P, _I, _I, _U, _P, _P, _I, _P],
+    "b200_all_gather_bf16": [_P, _P, _LL, _I, _I, _I, _P],
+    "b200_reduce_scatter_bf16_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
+    "b200_reduce_scatter_f32_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
 }
 _fn_cache = {}
 
@@ -196,6 +203,13 @@ def adamw_step(master, grad, exp_avg, exp_avg_sq, shadow, decay_chunks, lo, hi, 
           decay_chunks.data_ptr(), lo, hi, step, lr, beta1, beta2, eps, wd, _ptr(grad_scale), _stream())
 
 
+def adamw_step_ptr(master_ptr, grad_ptr, m_ptr, v_ptr, shadow_ptr, decay_ptr, lo, hi, step, lr, beta1, beta2, eps, wd,
+                   grad_scale_ptr):
+    """Raw-pointer form: sharded engines index ``grad``/``shadow`` through pre-offset base pointers."""
+    _call("b200_adamw", master_ptr, grad_ptr, m_ptr, v_ptr, shadow_ptr, decay_ptr, lo, hi, step, lr, beta1, beta2,
+          eps, wd, grad_scale_ptr, _stream())
+
+
 def sumsq(x_f32, lo, hi, out):
     _call("b200_sumsq", x_f32.data_ptr(), lo, hi, out.data_ptr(), _stream())
 
@@ -206,3 +220,44 @@ def clip_coef(sumsq_t, max_norm, pre_scale, scale_out, norm_out=None):
 
 def rng_advance(rng_state, delta=1):
     _call("b200_rng_advance", rng_state.data_ptr(), delta, _stream())
+
+
+# ----------------------------------------------------------------------------------------------- NVLink comm
+def ptr_array(ptrs):
+    """Host array of device pointers (one per rank) in the form the comm entry points take."""
+    return (C.c_void_p * len(ptrs))(*ptrs)
+
+
+def comm_barrier(pad_ptrs, rank, world, epoch):
+    _call("b200_comm_barrier", pad_ptrs, rank, world, epoch & 0xFFFFFFFF, _stream())
+
+
+def reduce_scatter_f32(grad_ptrs, dst, lo, hi, scale, sumsq, rank, world, max_ctas=0):
+    _call("b200_reduce_scatter_f32", grad_ptrs, dst.data_ptr(), lo, hi, scale, _ptr(sumsq), rank, world, max_ctas,
+          _stream())
+
+
+def adamw_bcast(master, grad, exp_avg, exp_avg_sq, shadow_ptrs, rank, world, decay_chunks, lo, hi, step, lr, beta1,
+                beta2, eps, wd, grad_scale, max_ctas=0):
+    _call("b200_adamw_bcast", master.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(),
+          shadow_ptrs, rank, world, decay_chunks.data_ptr(), lo, hi, step, lr, beta1, beta2, eps, wd,
+          _ptr(grad_scale), max_ctas, _stream())
+
+
+def allreduce_scalars(pad_ptrs, rank, world, epoch, inp, out, n):
+    _call("b200_allreduce_scalars", pad_ptrs, rank, world, epoch & 0xFFFFFFFF, inp.data_ptr(), out.data_ptr(), n,
+          _stream())
+
+
+def all_gather_bf16(shard_ptrs, dst, shard_elems, rank, world, max_ctas=0):
+    _call("b200_all_gather_bf16", shard_ptrs, dst.data_ptr(), shard_elems, rank, world, max_ctas, _stream())
+
+
+def reduce_scatter_bf16_accum(full_grad_ptrs, dst_shard, src_offset, n, scale, rank, world, max_ctas=0):
+    _call("b200_reduce_scatter_bf16_accum", full_grad_ptrs, dst_shard.data_ptr(), src_offset, n, scale, rank, world,
+          max_ctas, _stream())
+
+
+def reduce_scatter_f32_accum(full_grad_ptrs, dst_shard, src_offset, n, scale, rank, world, max_ctas=0):
+    _call("b200_reduce_scatter_f32_accum", full_grad_ptrs, dst_shard.data_ptr(), src_offset, n, scale, rank, world,
+          max_ctas, _stream())

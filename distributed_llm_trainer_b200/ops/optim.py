@@ -43,13 +43,19 @@ class FlatAdamW:
     (``param_groups[i]["lr"]``, ``step``, ``zero_grad``, ``state_dict``, ``load_state_dict``)."""
 
     def __init__(self, store: FlatParamStore, lr: float, betas=(0.9, 0.95), eps: float = 1e-8,
-                 weight_decay: float = 0.1, lo: int = 0, hi: Optional[int] = None, decay_norms: bool = False,
+                 weight_decay: float = 0.1, ranges: Optional[List] = None, decay_norms: bool = False,
                  layout: str = "ddp"):
         self.store = store
-        self.lo, self.hi = lo, store.total if hi is None else hi
+        # flat element ranges this rank owns (sharded engines pass their slices); state is stored
+        # back to back in range order
+        self.ranges = [(0, store.total)] if ranges is None else [(int(a), int(b)) for a, b in ranges]
+        self.state_offsets = []
+        n = 0
+        for a, b in self.ranges:
+            self.state_offsets.append(n)
+            n += b - a
         self.layout = layout            # "ddp" (two groups, int keys) or "fsdp" (one group, FQN keys)
         self.decay_norms = decay_norms  # reference FSDP decays every tensor (fsdp_trainer.py:338-343)
-        n = self.hi - self.lo
         dev = store.device
         self.exp_avg = torch.zeros(n, dtype=torch.float32, device=dev)
         self.exp_avg_sq = torch.zeros(n, dtype=torch.float32, device=dev)
@@ -83,44 +89,54 @@ class FlatAdamW:
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
         self.step_count += 1
         st = self.store
-        lo, hi = self.lo, self.hi
         scale = self.grad_scale if grad_scale is None else grad_scale
-        if st.device.type == "cuda":
-            kernels.adamw_step(st.master, st.grad, self.exp_avg, self.exp_avg_sq, st.shadow, self._decay,
-                               lo, hi, self.step_count, lr, b1, b2, eps, wd, scale)
-        else:
-            from ..parallel.flat import ALIGN
+        for (lo, hi), off in zip(self.ranges, self.state_offsets):
+            if hi <= lo:
+                continue
+            m, v = self.exp_avg[off: off + hi - lo], self.exp_avg_sq[off: off + hi - lo]
+            if st.device.type == "cuda":
+                kernels.adamw_step(st.master, st.grad, m, v, st.shadow, self._decay,
+                                   lo, hi, self.step_count, lr, b1, b2, eps, wd, scale)
+            else:
+                from ..parallel.flat import ALIGN
 
-            mask = self._decay.to(torch.float32).repeat_interleave(ALIGN)[lo:hi]
-            adamw_reference_(st.master[lo:hi], st.grad[lo:hi], self.exp_avg, self.exp_avg_sq, mask,
-                             self.step_count, lr, b1, b2, eps, wd, float(scale.item()),
-                             None if st.shadow is None else st.shadow[lo:hi])
+                mask = self._decay.to(torch.float32).repeat_interleave(ALIGN)[lo:hi]
+                adamw_reference_(st.master[lo:hi], st.grad[lo:hi], m, v, mask,
+                                 self.step_count, lr, b1, b2, eps, wd, float(scale.item()),
+                                 None if st.shadow is None else st.shadow[lo:hi])
 
     def zero_grad(self, set_to_none: bool = False) -> None:
         self.store.zero_grad()
 
-    # ---- state dict (full-range optimizers; sharded engines gather into a full one first) -------
-    def _slot_state(self, slot) -> Dict[str, torch.Tensor]:
-        a, b = slot.offset - self.lo, slot.offset - self.lo + slot.numel
-        return {
-            "step": torch.tensor(float(self.step_count)),
-            "exp_avg": self.exp_avg[a:b].view(slot.shape).clone(),
-            "exp_avg_sq": self.exp_avg_sq[a:b].view(slot.shape).clone(),
-        }
+    # ---- state dict --------------------------------------------------------------------------------
+    # Checkpoints always carry the FULL (unsharded) state in the reference's format.  A sharded
+    # optimizer is serialised by first assembling full flat exp_avg / exp_avg_sq buffers
+    # (``NVLinkGradSync`` / ``ShardedGPT`` gather them) and calling ``state_dict(full_m, full_v)``.
+    @property
+    def is_full(self) -> bool:
+        return self.ranges == [(0, self.store.total)]
 
-    def state_dict(self) -> Dict[str, Any]:
-        assert self.lo == 0 and self.hi == self.store.total, "gather the sharded state first"
+    def state_dict(self, full_exp_avg: Optional[torch.Tensor] = None,
+                   full_exp_avg_sq: Optional[torch.Tensor] = None) -> Dict[str, Any]:
+        if full_exp_avg is None:
+            assert self.is_full, "gather the sharded state first"
+            full_exp_avg, full_exp_avg_sq = self.exp_avg, self.exp_avg_sq
         slots = self.store.slots
         state: Dict[Any, Any] = {}
         if self.step_count > 0:
             for k, si in enumerate(self._order):
-                key = k if self.layout == "ddp" else slots[si].name
-                state[key] = self._slot_state(slots[si])
-        groups = [dict(g) for g in self.param_groups]
-        return {"state": state, "param_groups": groups}
+                sl = slots[si]
+                a, b = sl.offset, sl.offset + sl.numel
+                state[k if self.layout == "ddp" else sl.name] = {
+                    "step": torch.tensor(float(self.step_count)),
+                    "exp_avg": full_exp_avg[a:b].view(sl.shape).clone(),
+                    "exp_avg_sq": full_exp_avg_sq[a:b].view(sl.shape).clone(),
+                }
+        return {"state": state, "param_groups": [dict(g) for g in self.param_groups]}
 
     def load_state_dict(self, sd: Dict[str, Any]) -> None:
-        assert self.lo == 0 and self.hi == self.store.total, "scatter into shards after loading"
+        """Accepts either key style (int-keyed DDP layout or FQN-keyed FSDP layout); a sharded
+        optimizer keeps only the elements inside its owned ranges."""
         slots = self.store.slots
         state = sd.get("state", {})
         name_to_slot = {s.name: s for s in slots}
@@ -130,9 +146,12 @@ class FlatAdamW:
                 slot = name_to_slot[key]
             else:
                 slot = slots[self._order[int(key)]] if self.layout == "ddp" else slots[int(key)]
-            a, b = slot.offset, slot.offset + slot.numel
-            self.exp_avg[a:b].copy_(st["exp_avg"].reshape(-1))
-            self.exp_avg_sq[a:b].copy_(st["exp_avg_sq"].reshape(-1))
+            src_m, src_v = st["exp_avg"].reshape(-1), st["exp_avg_sq"].reshape(-1)
+            for (lo, hi), off in zip(self.ranges, self.state_offsets):
+                a, b = max(lo, slot.offset), min(hi, slot.offset + slot.numel)
+                if a < b:
+                    self.exp_avg[off + a - lo: off + b - lo].copy_(src_m[a - slot.offset: b - slot.offset])
+                    self.exp_avg_sq[off + a - lo: off + b - lo].copy_(src_v[a - slot.offset: b - slot.offset])
             steps.add(int(float(st["step"])))
         self.step_count = max(steps) if steps else 0
         for g, src in zip(self.param_groups, sd.get("param_groups", [])):

@@ -1,0 +1,104 @@
+"""NVLink communication runtime: peer-mapped ("symmetric") buffers, pointer tables, signal pads.
+
+Replaces what NCCL provides underneath torch DDP / FSDP in the reference (communicator init
+ddp_trainer.py:99, fsdp_trainer.py:128) for the hot collectives: every rank allocates a
+buffer with the library's raw allocator, exports a CUDA IPC handle, and maps every peer's buffer into
+its own address space, after which kernels load / store peer memory directly over NVLink
+(``csrc/comm.cu``).  ``torch.distributed`` (NCCL) is used only for the bootstrap exchange of the
+64-byte handles and for cold paths (checkpoint gathers).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import List, Optional
+
+import torch
+import torch.distributed as dist
+
+from ..ops import _lib
+from ..ops import kernels as K
+
+_DTYPE_STR = {torch.float32: "<f4", torch.int32: "<i4", torch.uint8: "|u1", torch.int16: "<i2"}
+
+
+class _RawCudaArray:
+    """Minimal ``__cuda_array_interface__`` carrier so torch can wrap a raw device pointer zero-copy."""
+
+    def __init__(self, ptr: int, numel: int, typestr: str):
+        self.__cuda_array_interface__ = {"shape": (numel,), "typestr": typestr, "data": (ptr, False), "version": 2,
+                                         "strides": None}
+
+
+def wrap_pointer(ptr: int, numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+    if dtype == torch.bfloat16:
+        return torch.as_tensor(_RawCudaArray(ptr, numel, "<i2"), device=device).view(torch.bfloat16)
+    return torch.as_tensor(_RawCudaArray(ptr, numel, _DTYPE_STR[dtype]), device=device)
+
+
+class SymmetricBuffer:
+    """One allocation per rank, all of them mapped into every rank.  ``local`` is a torch view of this
+    rank's copy; ``ptrs`` is the host pointer table (index = rank) the comm entry points take."""
+
+    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, group=None):
+        lib = _lib.lib()
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.numel, self.dtype, self.device = numel, dtype, device
+        itemsize = torch.empty((), dtype=dtype).element_size()
+        self.nbytes = (numel * itemsize + 255) // 256 * 256
+        p = C.c_void_p()
+        _lib.check(lib.b200_device_malloc(C.byref(p), C.c_size_t(self.nbytes)), "b200_device_malloc")
+        self._own_ptr = p.value
+        handle = (C.c_ubyte * 64)()
+        _lib.check(lib.b200_ipc_export(C.c_void_p(self._own_ptr), handle), "b200_ipc_export")
+        handles: List[Optional[bytes]] = [None] * self.world
+        dist.all_gather_object(handles, bytes(handle), group=group)
+        raw: List[int] = []
+        self._opened: List[int] = []
+        for r, h in enumerate(handles):
+            if r == self.rank:
+                raw.append(self._own_ptr)
+                continue
+            q = C.c_void_p()
+            buf = (C.c_ubyte * 64).from_buffer_copy(h)
+            _lib.check(lib.b200_ipc_open(buf, C.byref(q)), f"b200_ipc_open(rank {r})")
+            raw.append(q.value)
+            self._opened.append(q.value)
+        self.raw_ptrs = raw
+        self.ptrs = K.ptr_array(raw)
+        self.local = wrap_pointer(self._own_ptr, numel, dtype, device)
+        dist.barrier(group=group)
+
+    def offset_ptrs(self, byte_offset: int):
+        return K.ptr_array([p + byte_offset for p in self.raw_ptrs])
+
+    def close(self) -> None:
+        lib = _lib.lib()
+        for p in self._opened:
+            lib.b200_ipc_close(C.c_void_p(p))
+        self._opened = []
+        if self._own_ptr:
+            lib.b200_device_free(C.c_void_p(self._own_ptr))
+            self._own_ptr = 0
+
+
+class SignalPads:
+    """Per-rank flag area + the monotonically increasing epoch every waiting kernel is launched with."""
+
+    def __init__(self, device: torch.device, group=None):
+        nbytes = _lib.lib().b200_comm_pad_bytes()
+        self.buf = SymmetricBuffer(nbytes // 4, torch.int32, device, group)
+        self.rank, self.world = self.buf.rank, self.buf.world
+        self.epoch = 0
+
+    def next_epoch(self) -> int:
+        self.epoch += 1
+        return self.epoch
+
+    def barrier(self) -> None:
+        """Device-side barrier on the current stream (no host sync)."""
+        K.comm_barrier(self.buf.ptrs, self.rank, self.world, self.next_epoch())
+
+    def allreduce_scalars(self, inp: torch.Tensor, out: torch.Tensor, n: int) -> None:
+        K.allreduce_scalars(self.buf.ptrs, self.rank, self.world, self.next_epoch(), inp, out, n)

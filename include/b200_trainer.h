@@ -145,6 +145,37 @@ int b200_clip_coef(const float* sumsq, float max_norm, float pre_scale, float* s
 /* rng_state[1] += delta  (device-side offset bump: keeps dropout fresh under CUDA-graph replay) */
 int b200_rng_advance(unsigned long long* rng_state, unsigned long long delta, void* stream);
 
+/* ---------------------------------------------------------------- NVLink communication -------- */
+/* All of these take HOST arrays of `world` device pointers (one per rank, index = rank), each pointing
+ * at that rank's copy of a symmetric buffer mapped into this process (b200_ipc_open).  `pad_ptrs` are
+ * the signal pads (b200_comm_pad_bytes() bytes each, zero-initialised).  `epoch` must increase by one
+ * on every call that takes it, identically on all ranks.  Kernels that wait on peers are bounded by a
+ * 20 s device-side timeout and trap instead of hanging. */
+int b200_comm_pad_bytes(void);
+int b200_comm_barrier(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, void* stream);
+/* dst[lo:hi] = scale * sum_r grads_r[lo:hi]; sumsq[0] += |dst[lo:hi]|^2  (reference: DDP bucket all-reduce
+ * ddp_trainer.py:342 + clip_grad_norm_ :350, FSDP reduce_scatter fsdp_trainer.py:383) */
+int b200_reduce_scatter_f32(const void* const* grad_ptrs, float* dst, long long lo, long long hi, float scale,
+                            float* sumsq, int rank, int world, int max_ctas, void* stream);
+/* AdamW on the owned range, bf16 result stored into every rank's shadow buffer (reference: all-reduce
+ * second half + optimizer.step, ddp_trainer.py:342,356) */
+int b200_adamw_bcast(float* master, const float* grad, float* exp_avg, float* exp_avg_sq,
+                     const void* const* shadow_ptrs, int rank, int world, const uint8_t* decay_chunks, long long lo,
+                     long long hi, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                     const float* grad_scale, int max_ctas, void* stream);
+/* out[i] = sum_r in_r[i], i < n <= 8 (reference: FSDP.clip_grad_norm_ scalar all-reduce, fsdp_trainer.py:388) */
+int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, const float* in,
+                           float* out, int n, void* stream);
+/* dst[r*shard + i] = shard_r[i]  (reference: FSDP all_gather_into_tensor, fsdp_trainer.py:379,383) */
+int b200_all_gather_bf16(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
+                         int max_ctas, void* stream);
+/* dst_shard[i] += scale * sum_r full_grad_r[src_offset + i]  (reference: FSDP reduce_scatter_tensor,
+ * fsdp_trainer.py:383).  fp32 wire (exact) and bf16 wire (the reference's reduce_dtype) variants. */
+int b200_reduce_scatter_f32_accum(const void* const* full_grad_ptrs, float* dst_shard, long long src_offset,
+                                  long long n, float scale, int rank, int world, int max_ctas, void* stream);
+int b200_reduce_scatter_bf16_accum(const void* const* full_grad_ptrs, float* dst_shard, long long src_offset,
+                                   long long n, float scale, int rank, int world, int max_ctas, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
