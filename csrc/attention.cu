@@ -9,9 +9,11 @@
 // Forward CTA = (q block of 128 rows, head, batch), 6 warps:
 //   warp 0     TMA producer: Q once, K/V tiles through 2-stage rings
 //   warp 1     MMA issuer:   S_j = Q K_j^T  (TMEM, double buffered)  and  O_j = P_j V_j (TMEM, double buffered)
-//   warps 2-5  softmax: thread r owns query row r.  tcgen05.ld S row -> online softmax in the exp2
-//              domain -> dropout -> bf16 P tile written to 128B-swizzled smem (A operand of P V) ->
-//              running O kept in registers: o = o * alpha + O_j (no TMEM rescale pass).
+//   warps 2-9  softmax: two threads per query row, each owning 64 of the 128 score columns (two warps
+//              per scheduler hide the tcgen05.ld / MUFU latencies one warp cannot).  tcgen05.ld S ->
+//              online softmax in the exp2 domain (row max exchanged once per tile through smem) ->
+//              dropout -> bf16 P tile written to 128B-swizzled smem (A operand of P V) -> running O kept
+//              in registers: o = o * alpha + O_j (no TMEM rescale pass).
 // Backward CTA = (kv block, head, batch) looping over q blocks i >= j; five MMAs per pair:
 //   S = Q K^T, dP = dO V^T, dV += P~^T dO, dK += dS^T Q, dQ_i = dS K  (dQ reduced with red.global.add.f32)
 // P~ / dS tiles are written once to smem and consumed both K-major (dS K) and MN-major (P~^T dO,
@@ -64,10 +66,16 @@ struct FwdSmem {
   static constexpr int kV = kK + 2 * kTile;        // 2 stages
   static constexpr int kP = kV + 2 * kTile;        // 2 buffers x 32 KB
   static constexpr int kBars = kP + 2 * kPTile;
-  static constexpr int kTotal = kBars + 256 + 1024;
+  static constexpr int kXchg = kBars + 256;                 // float [2][2][128] row-max exchange
+  static constexpr int kTotal = kXchg + 2 * 2 * 128 * 4 + 1024;
 };
 
-__global__ void __launch_bounds__(192, 1)
+constexpr int kSoftmaxWarps = 8;
+constexpr int kAttnThreads = 64 + kSoftmaxWarps * 32;
+
+__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+
+__global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
@@ -101,10 +109,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       mbar_init(&v_full[i], 1);
       mbar_init(&v_empty[i], 1);
       mbar_init(&s_full[i], 1);
-      mbar_init(&s_free[i], 4);
-      mbar_init(&p_ready[i], 4);
+      mbar_init(&s_free[i], kSoftmaxWarps);
+      mbar_init(&p_ready[i], kSoftmaxWarps);
       mbar_init(&o_full[i], 1);
-      mbar_init(&o_free[i], 4);
+      mbar_init(&o_free[i], kSoftmaxWarps);
     }
     fence_barrier_init();
   }
@@ -175,6 +183,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     }
   } else {
     const int qd = warp & 3;
+    const int hf = (warp - 2) >> 2;               // which 64-column half of the score tile this thread owns
     const int r = qd * 32 + lane;                 // row within the q tile
     const int qrow = qi * kBlk + r;               // position in the sequence
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
@@ -183,11 +192,23 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
     const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
+    float* xchg = reinterpret_cast<float*>(smem + FwdSmem::kXchg);
 
     float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-    float o[kD];
+    float o[32];
 #pragma unroll
-    for (int e = 0; e < kD; ++e) o[e] = 0.f;
+    for (int e = 0; e < 32; ++e) o[e] = 0.f;
+
+    auto fold_o = [&](int pb, uint32_t parity, float alpha) {
+      mbar_wait(&o_full[pb], parity);
+      tc_fence_after();
+      uint32_t v[32];
+      __syncwarp();
+      tmem_ld_32x32b_x32(tO[pb] + lane_off + hf * 32, v);
+      tmem_ld_wait();
+#pragma unroll
+      for (int e = 0; e < 32; ++e) o[e] = o[e] * alpha + __uint_as_float(v[e]);
+    };
 
     for (int j = 0; j < nkv; ++j) {
       const int st = j & 1;
@@ -195,46 +216,48 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       const bool diag = (j == qi);
       mbar_wait(&s_full[st], ph);
       tc_fence_after();
-      // pass 1: row maximum
-      float mx = m;
+      // pass 1: maximum over this thread's 64 columns, then exchange with the partner thread
+      float mx = -INFINITY;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
         __syncwarp();
-        tmem_ld_32x32b_x32(tS[st] + lane_off + c * 32, v);
+        tmem_ld_32x32b_x32(tS[st] + lane_off + hf * 64 + c * 32, v);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 32; ++e) {
-          const float s = __uint_as_float(v[e]) * kScale2;
-          if (!diag || (c * 32 + e) <= r) mx = fmaxf(mx, s);
+          const float sc = __uint_as_float(v[e]) * kScale2;
+          if (!diag || (hf * 64 + c * 32 + e) <= r) mx = fmaxf(mx, sc);
         }
       }
+      xchg[(st * 2 + hf) * 128 + r] = mx;
+      softmax_bar_sync();
+      mx = fmaxf(fmaxf(mx, xchg[(st * 2 + (hf ^ 1)) * 128 + r]), m);
       const float m_use = (mx == -INFINITY) ? 0.f : mx;
       const float alpha = exp2f(m - m_use);
       l *= alpha;
       // pass 2: probabilities -> smem (bf16, dropout applied, unnormalised)
-      const uint32_t p_base = smem_u32(smem + FwdSmem::kP + st * kPTile);
+      const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + hf * kTile;
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t v[32];
         __syncwarp();
-        tmem_ld_32x32b_x32(tS[st] + lane_off + c * 32, v);
+        tmem_ld_32x32b_x32(tS[st] + lane_off + hf * 64 + c * 32, v);
         tmem_ld_wait();
-        const uint32_t sub = p_base + (c >> 1) * kTile;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint32_t keep = 0xFF;
-          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + c * 32 + g * 8) >> 3), thresh);
+          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + hf * 64 + c * 32 + g * 8) >> 3), thresh);
           float pv[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            const int col = c * 32 + g * 8 + e;
+            const int col = hf * 64 + c * 32 + g * 8 + e;
             float pe = exp2f(__uint_as_float(v[g * 8 + e]) * kScale2 - m_use);
             if (diag && col > r) pe = 0.f;
             l += pe;
             pv[e] = ((keep >> e) & 1) ? pe : 0.f;
           }
-          st_shared_v4(swz(sub, r, (c & 1) * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
+          st_shared_v4(swz(sub, r, c * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
                        pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
         }
       }
@@ -248,17 +271,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       // fold in O_{j-1}
       if (j > 0) {
         const int pb = (j - 1) & 1;
-        mbar_wait(&o_full[pb], ((j - 1) >> 1) & 1);
-        tc_fence_after();
-#pragma unroll
-        for (int c = 0; c < 2; ++c) {
-          uint32_t v[32];
-          __syncwarp();
-          tmem_ld_32x32b_x32(tO[pb] + lane_off + c * 32, v);
-          tmem_ld_wait();
-#pragma unroll
-          for (int e = 0; e < 32; ++e) o[c * 32 + e] = o[c * 32 + e] * alpha_prev + __uint_as_float(v[e]);
-        }
+        fold_o(pb, ((j - 1) >> 1) & 1, alpha_prev);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&o_free[pb]);
@@ -266,29 +279,21 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       alpha_prev = alpha;
       m = m_use;
     }
-    {
-      const int pb = (nkv - 1) & 1;
-      mbar_wait(&o_full[pb], ((nkv - 1) >> 1) & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        __syncwarp();
-        tmem_ld_32x32b_x32(tO[pb] + lane_off + c * 32, v);
-        tmem_ld_wait();
-#pragma unroll
-        for (int e = 0; e < 32; ++e) o[c * 32 + e] = o[c * 32 + e] * alpha_prev + __uint_as_float(v[e]);
-      }
-    }
+    fold_o((nkv - 1) & 1, ((nkv - 1) >> 1) & 1, alpha_prev);
+    // total row sum = the two column-halves' partial sums (same running max on both threads)
+    softmax_bar_sync();
+    xchg[hf * 128 + r] = l;
+    softmax_bar_sync();
+    l += xchg[(hf ^ 1) * 128 + r];
     if (qrow < p.S) {
       const float inv = (drop ? 1.f / (1.f - p.p_drop) : 1.f) / l;
-      __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD;
+      __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD + hf * 32;
 #pragma unroll
-      for (int g = 0; g < 8; ++g)
+      for (int g = 0; g < 4; ++g)
         *reinterpret_cast<uint4*>(dst + g * 8) =
             make_uint4(pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv), pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv),
                        pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv), pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv));
-      p.lse[size_t(b * p.H + hd) * p.S + qrow] = m + log2f(l);
+      if (hf == 0) p.lse[size_t(b * p.H + hd) * p.S + qrow] = m + log2f(l);
     }
   }
 
@@ -349,7 +354,7 @@ struct BwdSmem {
   static constexpr int kTotal = kBars + 256 + 1024;
 };
 
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                 const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -383,10 +388,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_init(&qdo_empty[i], 1);
     }
     mbar_init(sdp_full, 1);
-    mbar_init(s_free, 4);
-    mbar_init(pds_ready, 4);
+    mbar_init(s_free, kSoftmaxWarps);
+    mbar_init(pds_ready, kSoftmaxWarps);
     mbar_init(dq_full, 1);
-    mbar_init(dq_free, 4);
+    mbar_init(dq_free, kSoftmaxWarps);
     mbar_init(acc_full, 1);
     fence_barrier_init();
   }
@@ -458,6 +463,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
   } else {
     const int qd = warp & 3;
+    const int hf = (warp - 2) >> 2;   // two threads per row: each owns 64 kv columns / 32 head-dim columns
     const int r = qd * 32 + lane;
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
@@ -471,17 +477,16 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const int qrow = (j + it) * kBlk + r;
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
-      float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD;
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + hf * 32;
+      {
         uint32_t v[32];
         __syncwarp();
-        tmem_ld_32x32b_x32(tdQ + lane_off + c * 32, v);
+        tmem_ld_32x32b_x32(tdQ + lane_off + hf * 32, v);
         tmem_ld_wait();
         if (qrow < p.S) {
 #pragma unroll
           for (int g = 0; g < 8; ++g)
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + c * 32 + g * 4),
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 4),
                          "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
                          "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
                          : "memory");
@@ -505,21 +510,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
 #pragma unroll 1
-      for (int c = 0; c < 4; ++c) {
+      for (int c = 0; c < 2; ++c) {
         uint32_t sv[32], dv[32];
         __syncwarp();
-        tmem_ld_32x32b_x32(tS + lane_off + c * 32, sv);
-        tmem_ld_32x32b_x32(tdP + lane_off + c * 32, dv);
+        tmem_ld_32x32b_x32(tS + lane_off + hf * 64 + c * 32, sv);
+        tmem_ld_32x32b_x32(tdP + lane_off + hf * 64 + c * 32, dv);
         tmem_ld_wait();
-        const int sub = (c >> 1) * kTile;
+        const int sub = hf * kTile;
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
           uint32_t keep = 0xFF;
-          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + c * 32 + g * 8) >> 3), thresh);
+          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + hf * 64 + c * 32 + g * 8) >> 3), thresh);
           float pd[8], ds[8];
 #pragma unroll
           for (int e = 0; e < 8; ++e) {
-            const int col = c * 32 + g * 8 + e;
+            const int col = hf * 64 + c * 32 + g * 8 + e;
             float pe = exp2f(__uint_as_float(sv[g * 8 + e]) * kScale2 - lse2);
             if (diag && col > r) pe = 0.f;
             const bool k1 = (keep >> e) & 1;
@@ -527,7 +532,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             ds[e] = pe * (dpe - dl) * kScale;
             pd[e] = k1 ? pe * inv_keep : 0.f;
           }
-          const int cc = (c & 1) * 4 + g;
+          const int cc = c * 4 + g;
           st_shared_v4(swz(p_base + sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
                        pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
           st_shared_v4(swz(ds_base + sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
@@ -548,24 +553,23 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int kvrow = j * kBlk + r;
-    __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD;
+    __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD + hf * 32;
     __nv_bfloat16* dv_dst = dk_dst + h;
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
+    {
       uint32_t kv_[32], vv_[32];
       __syncwarp();
-      tmem_ld_32x32b_x32(tdK + lane_off + c * 32, kv_);
-      tmem_ld_32x32b_x32(tdV + lane_off + c * 32, vv_);
+      tmem_ld_32x32b_x32(tdK + lane_off + hf * 32, kv_);
+      tmem_ld_32x32b_x32(tdV + lane_off + hf * 32, vv_);
       tmem_ld_wait();
       if (kvrow < p.S) {
 #pragma unroll
         for (int g = 0; g < 4; ++g) {
-          *reinterpret_cast<uint4*>(dk_dst + c * 32 + g * 8) = make_uint4(
+          *reinterpret_cast<uint4*>(dk_dst + g * 8) = make_uint4(
               pack_bf16x2(__uint_as_float(kv_[g * 8 + 0]), __uint_as_float(kv_[g * 8 + 1])),
               pack_bf16x2(__uint_as_float(kv_[g * 8 + 2]), __uint_as_float(kv_[g * 8 + 3])),
               pack_bf16x2(__uint_as_float(kv_[g * 8 + 4]), __uint_as_float(kv_[g * 8 + 5])),
               pack_bf16x2(__uint_as_float(kv_[g * 8 + 6]), __uint_as_float(kv_[g * 8 + 7])));
-          *reinterpret_cast<uint4*>(dv_dst + c * 32 + g * 8) = make_uint4(
+          *reinterpret_cast<uint4*>(dv_dst + g * 8) = make_uint4(
               pack_bf16x2(__uint_as_float(vv_[g * 8 + 0]), __uint_as_float(vv_[g * 8 + 1])),
               pack_bf16x2(__uint_as_float(vv_[g * 8 + 2]), __uint_as_float(vv_[g * 8 + 3])),
               pack_bf16x2(__uint_as_float(vv_[g * 8 + 4]), __uint_as_float(vv_[g * 8 + 5])),
@@ -607,7 +611,7 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
     configured = true;
   }
   dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
-  attn_fwd_kernel<<<grid, 192, FwdSmem::kTotal, STREAM(stream)>>>(tm, p);
+  attn_fwd_kernel<<<grid, kAttnThreads, FwdSmem::kTotal, STREAM(stream)>>>(tm, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -639,7 +643,7 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
     configured = true;
   }
   dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
-  attn_bwd_kernel<<<grid, 192, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
+  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);
   attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);

@@ -214,6 +214,15 @@ __global__ void dropout_mask_kernel(uint8_t* __restrict__ mask, long long groups
   for (int e = 0; e < 8; ++e) mask[8 * g + e] = (keep >> e) & 1;
 }
 
+// ------------------------------------------------------------------------------------------------ cast
+__global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n8) {
+  const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (i >= n8) return;
+  const float4 a = reinterpret_cast<const float4*>(src)[2 * i], b = reinterpret_cast<const float4*>(src)[2 * i + 1];
+  reinterpret_cast<uint4*>(dst)[i] =
+      make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(b.x, b.y), pack_bf16x2(b.z, b.w));
+}
+
 // ------------------------------------------------------------------------------------------------ rotary
 // thread per (row, head, 8-wide group of the first half); pairs column j with j+32 (head_dim 64)
 __global__ void rope_inplace_kernel(__nv_bfloat16* __restrict__ qkv, const float* __restrict__ cs,
@@ -361,6 +370,14 @@ int b200_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned
   B200_REQUIRE(cols % 8 == 0, "dropout_mask: cols %% 8 != 0");
   const long long groups = (long long)rows * (cols / 8);
   dropout_mask_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(mask, groups, p, rng, rs);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_cast_f32_bf16(const float* src, void* dst, long long n, void* stream) {
+  B200_REQUIRE(n % 8 == 0, "cast: n %% 8 != 0");
+  if (n == 0) return 0;
+  cast_f32_bf16_kernel<<<(unsigned)((n / 8 + 255) / 256), 256, 0, STREAM(stream)>>>(src, (__nv_bfloat16*)dst, n / 8);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -469,7 +469,9 @@ extern "C" int b200_gemm_bf16(const b200_gemm_args* a, void* stream_) {
       double useful = double(a->M) * a->N;
       return useful / (double(waves) * sms * BM * w);
     };
-    bn = eff(256) >= eff(128) * 0.98 ? 256 : 128;
+    // Measured on B200 (benchmarks/bench_gemm.py): the 256-wide tile wins even at 65% wave efficiency
+    // (N = 768) because it halves A re-reads from L2; only fall back when it wastes most of a wave.
+    bn = (a->N >= 256 && eff(256) >= eff(128) * 0.6) ? 256 : 128;
   }
   if (a->epilogue == EPI_ROPE_BF16) B200_REQUIRE(a->rope_cols % 64 == 0, "gemm: rope_cols must be a multiple of 64");
   if (a->epilogue == EPI_SWIGLU)

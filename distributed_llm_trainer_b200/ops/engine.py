@@ -86,6 +86,7 @@ class _Workspace:
         self.loss_sum = torch.zeros(1, dtype=f32, device=dev)
         if training:
             self.dxnf = torch.empty(M, h, dtype=bf, device=dev)
+            self.dxnf32 = torch.empty(M, h, dtype=f32, device=dev)
             self.dx = torch.empty(M, h, dtype=f32, device=dev)
             self.dy = torch.empty(M, h, dtype=bf, device=dev)
             self.dxn = torch.empty(M, h, dtype=bf, device=dev)
@@ -245,15 +246,24 @@ class FusedGPTEngine:
         scale = loss_scale / max(n_valid, 1)
         labels = ws.labels.view(-1)
         w = self._emb_weight()
+        if with_grad:
+            ws.dxnf32.zero_()
         for r0 in range(0, M, ws.lm_rows):
             r1 = min(M, r0 + ws.lm_rows)
             logits = ws.logits[: r1 - r0]
             K.gemm(ws.xnf[r0:r1], w, logits, tile_n=256, max_ctas=self.max_ctas, N=self.vocab_padded)
             K.ce_fwd_bwd(logits, labels[r0:r1], ws.loss_sum, V, scale, scale)
             if with_grad:
-                K.gemm(logits, w, ws.dxnf[r0:r1], b_mn=True, max_ctas=self.max_ctas, K=V)
+                # dX chunk: [rows, V] x [V, h] has only rows/128 * h/256 output tiles (21 for 896 x 768) but a
+                # 50k-long contraction, so split K across the SMs and reduce in fp32 (cast to bf16 afterwards)
+                tiles = ((r1 - r0 + 127) // 128) * ((ws.dxnf32.shape[1] + 255) // 256)
+                split = max(1, min(16, self.sm_count // max(tiles, 1)))
+                K.gemm(logits, w, ws.dxnf32[r0:r1], b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split, tile_n=256,
+                       max_ctas=self.max_ctas, K=V)
                 K.gemm(logits, ws.xnf[r0:r1], self.g_emb, a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, tile_n=256,
                        max_ctas=self.max_ctas, M=V, K=r1 - r0)
+        if with_grad:
+            K.cast_f32_bf16(ws.dxnf32, ws.dxnf)
 
     def _emb_weight(self) -> torch.Tensor:
         return self.w_emb

@@ -43,6 +43,7 @@ _SIGS = {
     "b200_dropout_bwd_cast": [_P, _P, _I, _I, _F, _P, _U, _P],
     "b200_dropout_mask": [_P, _I, _I, _F, _P, _U, _P],
     "b200_rope_inplace": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
+    "b200_cast_f32_bf16": [_P, _P, _LL, _P],
     "b200_swiglu_fwd": [_P, _P, _I, _I, _P],
     "b200_swiglu_bwd": [_P, _P, _P, _I, _I, _P],
     "b200_attn_fwd": [_P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
@@ -165,6 +166,10 @@ def rope_inplace(qkv_bf16, cos, sin, rope_cols, seq_len, inverse=False):
     rows = qkv_bf16.shape[0]
     _call("b200_rope_inplace", qkv_bf16.data_ptr(), cos.data_ptr(), sin.data_ptr(), rows, qkv_bf16.stride(0),
           rope_cols, seq_len, int(inverse), _stream())
+
+
+def cast_f32_bf16(src_f32, dst_bf16):
+    _call("b200_cast_f32_bf16", src_f32.data_ptr(), dst_bf16.data_ptr(), src_f32.numel(), _stream())
 
 
 def swiglu_fwd(gu_bf16, act_bf16):

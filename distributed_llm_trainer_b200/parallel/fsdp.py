@@ -34,6 +34,11 @@ from .flat import ALIGN, FlatParamStore
 
 def _gather_ranges(all_ranges, world, local_pieces: List[torch.Tensor], out_full: torch.Tensor, group=None) -> None:
     """all-gather of ragged per-rank slices into a full flat buffer (cold path / torch path)."""
+    if world == 1:
+        for (a, b), t in zip(all_ranges[0], local_pieces):
+            if out_full[a:b].data_ptr() != t.data_ptr():
+                out_full[a:b].copy_(t.reshape(-1))
+        return
     sizes = [sum(b - a for a, b in rr) for rr in all_ranges]
     mx = max(sizes)
     mine = torch.zeros(mx, dtype=out_full.dtype, device=out_full.device)

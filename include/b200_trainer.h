@@ -100,6 +100,9 @@ int b200_dropout_bwd_cast(const float* dx, void* dy_bf16, int rows, int cols, fl
 int b200_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned long long* rng_state,
                       unsigned int rng_stream, void* stream);
 
+/* dst(bf16)[i] = src(fp32)[i]; used after split-K fp32 accumulation (reference: autocast's _to_copy casts, G11) */
+int b200_cast_f32_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+
 /* In-place rotary embedding on the q and k column ranges of a packed [rows, 3h] bf16 tensor.
  * inverse != 0 applies the transposed rotation (backward).  Unfused companion of B200_EPI_ROPE_BF16. */
 int b200_rope_inplace(void* qkv_bf16, const float* cos, const float* sin, int rows, int ld, int rope_cols,
