@@ -1,0 +1,269 @@
+"""Worker launched under torchrun by test_distributed_cpu.py (gloo, CPU) and test_multi_gpu.py (NCCL bootstrap
++ NVLink kernels).  Each mode asserts on every rank and exits non-zero on failure.
+
+    torchrun --nproc-per-node 2 tests/dist_worker.py <mode> [tmpdir]
+"""
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+import torch.distributed as dist  # noqa: E402
+
+from distributed_llm_trainer_b200.models import GPT, GPTConfig  # noqa: E402
+from distributed_llm_trainer_b200.training.config import FSDPConfig, TrainingConfig  # noqa: E402
+from distributed_llm_trainer_b200.training.ddp_trainer import DistributedTrainer  # noqa: E402
+from distributed_llm_trainer_b200.training.fsdp_trainer import FSDPTrainer  # noqa: E402
+
+GPU = torch.cuda.is_available()
+CFG = dict(vocab_size=512, hidden_size=128, num_layers=2, num_heads=2, max_seq_len=128, dropout=0.0,
+           attention_dropout=0.0)
+MP = "bf16" if GPU else "fp32"
+BACKEND = "nccl" if GPU else "gloo"
+
+
+def batches(n, rows, seed=11):
+    g = torch.Generator().manual_seed(seed)
+    return [torch.randint(0, 512, (rows, 128), generator=g) for _ in range(n)]
+
+
+def close(a, b, tol, what):
+    err = (a.float() - b.float()).abs().max().item()
+    ref = b.float().abs().max().item() + 1e-12
+    assert err <= tol * ref, f"{what}: max err {err:.3e} vs scale {ref:.3e} (tol {tol})"
+
+
+def all_ranks_equal(t, what):
+    ws = dist.get_world_size()
+    got = [torch.empty_like(t) for _ in range(ws)]
+    dist.all_gather(got, t.contiguous())
+    for r in range(1, ws):
+        assert torch.equal(got[0], got[r]), f"{what}: rank {r} differs from rank 0"
+
+
+def single_process_reference(kind, world, ga, steps, strategy="FULL_SHARD"):
+    """What one process computes for the same global batch: world*ga micro-steps per optimizer step."""
+    os_rank = os.environ.pop("RANK")
+    try:
+        torch.manual_seed(0)
+        model = GPT(GPTConfig(**CFG))
+        if kind == "ddp":
+            tr = _SoloDDP(model, ga * world)
+        else:
+            tr = _SoloFSDP(model, ga * world, strategy)
+    finally:
+        os.environ["RANK"] = os_rank
+    return tr
+
+
+class _Solo:
+    """Build a trainer object without touching torch.distributed (bypasses _setup_distributed)."""
+
+
+def _solo_common(cls, tr, model):
+    tr.distributed, tr.rank, tr.world_size, tr.local_rank, tr.is_main_process = False, 0, 1, int(
+        os.environ.get("LOCAL_RANK", 0)), False
+    tr._setup_device()
+    tr._setup_model(model)
+    tr._setup_optimizer()
+    tr.global_step, tr.tokens_seen = 0, 0
+    tr.last_grad_norm = None
+    return tr
+
+
+def _SoloDDP(model, ga):
+    tr = DistributedTrainer.__new__(DistributedTrainer)
+    tr.model_config = GPTConfig(**CFG)
+    tr.training_config = TrainingConfig(batch_size=2, gradient_accumulation_steps=ga, max_steps=50, warmup_steps=2,
+                                        mixed_precision=MP, seed=0)
+    return _solo_common(DistributedTrainer, tr, model)
+
+
+def _SoloFSDP(model, ga, strategy):
+    tr = FSDPTrainer.__new__(FSDPTrainer)
+    tr.model_config = GPTConfig(**CFG)
+    tr.training_config = TrainingConfig.fsdp_defaults(batch_size=2, gradient_accumulation_steps=ga, max_steps=50,
+                                                      warmup_steps=2, seed=0)
+    tr.fsdp_config = FSDPConfig(sharding_strategy=strategy, mixed_precision=MP, activation_checkpointing=True)
+    return _solo_common(FSDPTrainer, tr, model)
+
+
+def interleave(per_rank):
+    """Global batch in the order the solo run must see it: micro-step m of rank r -> position r*ga + m is not
+    required (sum is order independent); we simply concatenate the ranks' batches."""
+    return torch.cat(per_rank, dim=0)
+
+
+# ------------------------------------------------------------------------------------------------ modes
+def mode_ddp(tmp):
+    ga, steps = 2, 3
+    tcfg = TrainingConfig(batch_size=2, gradient_accumulation_steps=ga, max_steps=50, warmup_steps=2,
+                          mixed_precision=MP, seed=0, backend=BACKEND, checkpoint_dir=tmp)
+    tr = DistributedTrainer(GPTConfig(**CFG), tcfg)
+    rank, world = tr.rank, tr.world_size
+    solo = single_process_reference("ddp", world, ga, steps)
+    solo.raw_model.load_state_dict(tr.raw_model.state_dict())
+    if solo.engine is not None:
+        solo.engine.store.refresh_shadow()
+    data = [batches(steps, 2 * ga, seed=100 + r) for r in range(world)]
+    for s in range(steps):
+        out = tr.train_step({"input_ids": data[rank][s]})
+        ref = solo.train_step({"input_ids": interleave([data[r][s] for r in range(world)])})
+        lt = torch.tensor([out["loss"]], device=tr.device)
+        dist.all_reduce(lt)
+        assert abs(lt.item() / world - ref["loss"]) < (2e-2 if GPU else 1e-5) * abs(ref["loss"]), (lt.item() / world, ref)
+        assert out["tokens"] == ref["tokens"]
+    if tr.grad_sync is not None:
+        tr.grad_sync.gather_master_and_state()
+        all_ranks_equal(tr.engine.store.shadow, "bf16 shadow params")
+    for (n, p), (_, q) in zip(tr.raw_model.named_parameters(), solo.raw_model.named_parameters()):
+        close(p.detach(), q.detach(), 2e-2 if GPU else 1e-5, n)
+        all_ranks_equal(p.detach(), n)
+    # checkpoint: collective save, reference layout, reload into a fresh trainer
+    path = os.path.join(tmp, "ddp.pt")
+    tr.save_checkpoint(path)
+    dist.barrier()
+    ck = torch.load(path, map_location="cpu", weights_only=False)
+    assert ck["global_step"] == steps and len(ck["optimizer"]["param_groups"]) == 2
+    assert len(ck["optimizer"]["state"]) == len(list(tr.raw_model.parameters()))
+    tr2 = DistributedTrainer(GPTConfig(**CFG), TrainingConfig(batch_size=2, gradient_accumulation_steps=ga,
+                                                              max_steps=50, warmup_steps=2, mixed_precision=MP, seed=5,
+                                                              backend=BACKEND, resume_from=path))
+    nb = batches(1, 2 * ga, seed=500 + rank)[0]
+    a, b = tr.train_step({"input_ids": nb}), tr2.train_step({"input_ids": nb})
+    assert abs(a["loss"] - b["loss"]) < (1e-2 if GPU else 1e-5) * abs(a["loss"]), (a, b)
+
+
+def mode_fsdp(tmp, strategy):
+    ga, steps = 2, 3
+    tcfg = TrainingConfig.fsdp_defaults(batch_size=2, gradient_accumulation_steps=ga, max_steps=50, warmup_steps=2,
+                                        seed=0, backend=BACKEND, checkpoint_dir=tmp)
+    fcfg = FSDPConfig(sharding_strategy=strategy, mixed_precision=MP, activation_checkpointing=True)
+    tr = FSDPTrainer(GPTConfig(**CFG), tcfg, fcfg)
+    rank, world = tr.rank, tr.world_size
+    solo = single_process_reference("fsdp", world, ga, steps, strategy)
+    solo.model.load_state_dict(tr.model.state_dict())
+    if solo.engine is not None:
+        solo.engine.store.refresh_shadow()
+    data = [batches(steps, 2 * ga, seed=200 + r) for r in range(world)]
+    for s in range(steps):
+        out = tr.train_step({"input_ids": data[rank][s]})
+        ref = solo.train_step({"input_ids": interleave([data[r][s] for r in range(world)])})
+        lt = torch.tensor([out["loss"]], device=tr.device)
+        dist.all_reduce(lt)
+        assert abs(lt.item() / world - ref["loss"]) < (2e-2 if GPU else 1e-5) * abs(ref["loss"]), (lt.item() / world, ref)
+    path = os.path.join(tmp, f"fsdp_{strategy}.pt")
+    tr.save_checkpoint(path)          # gathers full fp32 parameters + optimizer state (collective)
+    for (n, p), (_, q) in zip(tr.model.named_parameters(), solo.model.named_parameters()):
+        close(p.detach(), q.detach(), 2e-2 if GPU else 1e-5, n)
+    ck = torch.load(path, map_location="cpu", weights_only=False)
+    assert ck["fsdp_config"]["sharding_strategy"] == strategy
+    assert set(ck["optimizer"]["state"]) == {n for n, _ in solo.model.named_parameters()}
+    solo_sd = solo.optimizer.state_dict() if solo.optimizer.is_full else None
+    if solo_sd is not None:
+        for k, v in ck["optimizer"]["state"].items():
+            close(v["exp_avg"], solo_sd["state"][k]["exp_avg"].cpu(), 5e-2 if GPU else 1e-5, f"exp_avg {k}")
+    tr2 = FSDPTrainer(GPTConfig(**CFG), TrainingConfig.fsdp_defaults(batch_size=2, gradient_accumulation_steps=ga,
+                                                                    max_steps=50, warmup_steps=2, seed=9,
+                                                                    backend=BACKEND, resume_from=path), fcfg)
+    nb = batches(1, 2 * ga, seed=600 + rank)[0]
+    a, b = tr.train_step({"input_ids": nb}), tr2.train_step({"input_ids": nb})
+    assert abs(a["loss"] - b["loss"]) < (1e-2 if GPU else 1e-5) * abs(a["loss"]), (a, b)
+
+
+def mode_comm(tmp):
+    """NVLink comm kernels vs torch.distributed collectives (GPU only)."""
+    from distributed_llm_trainer_b200.ops import kernels as K
+    from distributed_llm_trainer_b200.parallel.comm import SignalPads, SymmetricBuffer
+
+    dist.init_process_group("nccl", device_id=torch.device(f"cuda:{int(os.environ['LOCAL_RANK'])}"))
+    rank, world = dist.get_rank(), dist.get_world_size()
+    dev = torch.device(f"cuda:{int(os.environ['LOCAL_RANK'])}")
+    torch.cuda.set_device(dev)
+    pads = SignalPads(dev)
+    n = 128 * 1000 * world
+    g = SymmetricBuffer(n, torch.float32, dev)
+    torch.manual_seed(rank)
+    g.local.copy_(torch.randn(n, device=dev))
+    want = g.local.clone()
+    dist.all_reduce(want)
+    part = n // world
+    lo, hi = rank * part, (rank + 1) * part
+    sumsq = torch.zeros(1, device=dev)
+    torch.cuda.synchronize()
+    for it in range(20):                      # stress the epoch protocol
+        pads.barrier()
+    pads.barrier()
+    K.reduce_scatter_f32(g.ptrs, g.local, lo, hi, 1.0 / world, sumsq, rank, world)
+    pads.barrier()
+    torch.cuda.synchronize()
+    close(g.local[lo:hi], want[lo:hi] / world, 1e-6, "reduce_scatter_f32")
+    assert abs(sumsq.item() - (want[lo:hi] / world).pow(2).sum().item()) < 1e-3 * sumsq.item()
+    tot_in, tot = torch.zeros(8, device=dev), torch.zeros(8, device=dev)
+    tot_in[0], tot_in[1] = float(rank + 1), 2.0
+    for _ in range(5):
+        pads.allreduce_scalars(tot_in, tot, 2)
+    torch.cuda.synchronize()
+    assert tot[0].item() == world * (world + 1) / 2 and tot[1].item() == 2.0 * world
+    # all-gather (bf16) by P2P pull
+    shard = SymmetricBuffer(4096, torch.bfloat16, dev)
+    shard.local.copy_((torch.arange(4096, device=dev) % 251 + rank * 7).to(torch.bfloat16))
+    full = torch.zeros(4096 * world, dtype=torch.bfloat16, device=dev)
+    pads.barrier()
+    K.all_gather_bf16(shard.ptrs, full, 4096, rank, world)
+    pads.barrier()
+    torch.cuda.synchronize()
+    exp = [torch.empty(4096, dtype=torch.bfloat16, device=dev) for _ in range(world)]
+    dist.all_gather(exp, shard.local.clone())
+    assert torch.equal(full, torch.cat(exp))
+    # fused AdamW + broadcast: every rank's shadow gets every rank's slice
+    sh = SymmetricBuffer(n, torch.bfloat16, dev)
+    master = torch.ones(n, device=dev)
+    m, v = torch.zeros(part, device=dev), torch.zeros(part, device=dev)
+    decay = torch.ones(n // 128, dtype=torch.uint8, device=dev)
+    scale = torch.ones(1, device=dev)
+    pads.barrier()
+    K.adamw_bcast(master, g.local, m, v, sh.ptrs, rank, world, decay, lo, hi, 1, 1e-2, 0.9, 0.95, 1e-8, 0.1, scale)
+    pads.barrier()
+    torch.cuda.synchronize()
+    mine = master[lo:hi].to(torch.bfloat16)
+    got = [torch.empty(part, dtype=torch.bfloat16, device=dev) for _ in range(world)]
+    dist.all_gather(got, mine)
+    assert torch.equal(sh.local, torch.cat(got)), "adamw_bcast: shadow mismatch"
+    # staging-buffer reduce-scatter with accumulation (FSDP)
+    acc = torch.ones(part, device=dev)
+    pads.barrier()
+    K.reduce_scatter_f32_accum(g.ptrs, acc, lo, part, 0.5, rank, world)
+    pads.barrier()
+    torch.cuda.synchronize()
+    gsum = g.local.clone()
+    dist.all_reduce(gsum)
+    close(acc, 1 + 0.5 * gsum[lo:hi], 1e-5, "reduce_scatter_f32_accum")
+    dist.barrier()
+    for b in (g, shard, sh, pads.buf):
+        b.close()
+
+
+def main():
+    mode = sys.argv[1]
+    tmp = sys.argv[2] if len(sys.argv) > 2 else "/tmp/b200_dist_test"
+    os.makedirs(tmp, exist_ok=True)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    if mode == "ddp":
+        mode_ddp(tmp)
+    elif mode.startswith("fsdp"):
+        mode_fsdp(tmp, mode.split(":")[1])
+    elif mode == "comm":
+        mode_comm(tmp)
+    else:
+        raise SystemExit(f"unknown mode {mode}")
+    if dist.is_initialized():
+        dist.barrier()
+        dist.destroy_process_group()
+    print(f"rank {os.environ.get('RANK')} mode {mode} OK")
+
+
+if __name__ == "__main__":
+    main()
