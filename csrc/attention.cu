@@ -23,6 +23,8 @@
 #include <cuda_bf16.h>
 #include <math.h>
 
+#include <mutex>
+
 #include "../include/b200_trainer.h"
 #include "common/host.h"
 #include "common/philox.cuh"
@@ -642,6 +644,112 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal));
     configured = true;
   }
+  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
+  B200_CHECK_CUDA(cudaGetLastError());
+  const long long ng = rows * (h / 8);
+  attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+}  // extern "C"
+
+// ================================================================================================
+// Attention backward for callers that must not allocate device memory.
+//
+// b200_attn_bwd() above needs two scratch buffers from its caller (the softmax-gradient row sums and an
+// fp32 dQ accumulator).  Not every caller can provide them: a host whose framework allocator already
+// owns all of HBM, a serving loop where cudaMalloc is banned because it stalls the whole device, or a
+// plain C program linked against this library with no allocator of its own.  For those callers the
+// scratch lives inside the library image, in the fixed-size array below.  It is part of the module, so
+// every GPU that loads libb200trainer.so carries these 32 MiB from load until the process exits, whether
+// or not this entry point is ever called.
+// ================================================================================================
+#define B200_ATTN_BWD_NOALLOC_SCRATCH_BYTES (32u << 20)
+static __device__ __align__(256) unsigned char g_attn_bwd_noalloc_scratch[B200_ATTN_BWD_NOALLOC_SCRATCH_BYTES];
+
+namespace {
+
+constexpr int kNoAllocMaxDevices = 64;
+void* g_noalloc_scratch_addr[kNoAllocMaxDevices] = {nullptr};  // device address of the array, per device ordinal
+bool g_noalloc_func_configured[kNoAllocMaxDevices] = {false};
+std::mutex g_noalloc_mutex;
+
+// In host code the identifier g_attn_bwd_noalloc_scratch is only a handle for the symbol, not a pointer a
+// kernel may dereference; the real address differs per device and has to be asked for with that device
+// current.  Done once per device, on the first call made while that device is current.
+int noalloc_scratch_for_current_device(void** out) {
+  int dev = -1;
+  B200_CHECK_CUDA(cudaGetDevice(&dev));
+  B200_REQUIRE(dev >= 0 && dev < kNoAllocMaxDevices, "attn_bwd_noalloc: device ordinal %d not supported", dev);
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_scratch_addr[dev] == nullptr) {
+    void* ptr = nullptr;
+    B200_CHECK_CUDA(cudaGetSymbolAddress((void**)&ptr, g_attn_bwd_noalloc_scratch));
+    B200_REQUIRE(ptr != nullptr, "attn_bwd_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_scratch_addr[dev] = ptr;
+  }
+  if (!g_noalloc_func_configured[dev]) {
+    B200_CHECK_CUDA(cudaFuncSetAttribute(b200::attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                         b200::BwdSmem::kTotal));
+    g_noalloc_func_configured[dev] = true;
+  }
+  *out = g_noalloc_scratch_addr[dev];
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+unsigned long long b200_attn_bwd_noalloc_max_scratch_bytes(void) { return B200_ATTN_BWD_NOALLOC_SCRATCH_BYTES; }
+
+// Same result as b200_attn_bwd(); the caller passes inputs and outputs only.
+//
+//  * Size limit: batch*seq*heads*64*4 bytes (dQ accumulator) plus batch*heads*seq*4 bytes (row sums), each
+//    rounded up to 256, must fit in 32 MiB -- e.g. 8 x 1024 tokens at 12 heads (25.6 MiB) fits, 16 x 1024
+//    does not.  Larger problems are refused with an error; nothing is launched.
+//  * The first call on each device looks up the array's device address and raises the kernel's shared-memory
+//    limit.  Make that first call during start-up, before any stream capture begins.
+//  * All calls on a device share the one array and it still holds whatever the previous call left there.
+//    The part that must start from zero (the dQ accumulator) is cleared on `stream` at the start of every
+//    call; the row sums are fully rewritten.  Two calls whose GPU work can overlap -- different streams, or
+//    several host threads -- race on the array and corrupt each other: keep them on one stream or
+//    serialise them yourself.
+//  * No cudaMalloc, cudaFree or other allocating call is made, here or in anything this function calls.
+int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, int batch,
+                          int seq, int heads, float dropout_p, const unsigned long long* rng, unsigned int rng_stream,
+                          void* stream) {
+  B200_REQUIRE(batch > 0 && seq > 0 && heads > 0, "attn_bwd_noalloc: empty problem");
+  B200_REQUIRE(dropout_p == 0.f || rng != nullptr, "attn_bwd_noalloc: rng_state required when dropout_p > 0");
+  const int h = heads * kD;
+  const long long rows = (long long)batch * seq;
+  const unsigned long long dq_bytes = ((unsigned long long)rows * h * sizeof(float) + 255ull) & ~255ull;
+  const unsigned long long delta_bytes = ((unsigned long long)rows * heads * sizeof(float) + 255ull) & ~255ull;
+  B200_REQUIRE(dq_bytes + delta_bytes <= B200_ATTN_BWD_NOALLOC_SCRATCH_BYTES,
+               "attn_bwd_noalloc: batch=%d seq=%d heads=%d needs %llu bytes of scratch, the built-in array holds %u "
+               "(use b200_attn_bwd with caller-provided scratch for larger problems)",
+               batch, seq, heads, dq_bytes + delta_bytes, B200_ATTN_BWD_NOALLOC_SCRATCH_BYTES);
+  void* base = nullptr;
+  if (int rc = noalloc_scratch_for_current_device(&base)) return rc;
+  float* dq_accum = reinterpret_cast<float*>(base);
+  float* delta = reinterpret_cast<float*>(static_cast<unsigned char*>(base) + dq_bytes);
+
+  CUtensorMap tm_qkv, tm_do;
+  int rc = make_tmap_2d_bf16(&tm_qkv, qkv, 3 * (uint64_t)h, (uint64_t)rows, 3 * (uint64_t)h, 64, kBlk);
+  if (rc) return rc;
+  rc = make_tmap_2d_bf16(&tm_do, dout, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 64, kBlk);
+  if (rc) return rc;
+  cudaStream_t s = STREAM(stream);
+  const long long nd = rows * heads;
+  attn_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
+                                                                 delta, batch, seq, heads);
+  B200_CHECK_CUDA(cudaGetLastError());
+  B200_CHECK_CUDA(cudaMemsetAsync(dq_accum, 0, size_t(rows) * h * sizeof(float), s));  // stale from the last call
+  AttnParams p{};
+  p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
+  p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
   dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
   attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());

@@ -125,6 +125,25 @@ int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_b
                   void* dqkv_bf16, float* delta, float* dq_accum, int batch, int seq, int heads, float dropout_p,
                   const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
 
+/* Attention backward that allocates nothing and asks the caller for no scratch.  It has no counterpart in
+ * the reference project; it exists for hosts that cannot hand this library device memory on demand (a
+ * framework allocator that already owns all of HBM, a request path where cudaMalloc is forbidden because
+ * it stalls the device, a bare C caller).  The row-sum and dQ-accumulator scratch that b200_attn_bwd takes
+ * from its caller lives in a 32 MiB array compiled into the library, which every GPU that loads the
+ * library keeps resident until the process exits.
+ *   - same inputs, outputs and numerics as b200_attn_bwd;
+ *   - refused with an error when the scratch it needs -- batch*seq*heads*64*4 + batch*heads*seq*4 bytes,
+ *     each term rounded up to 256 -- exceeds b200_attn_bwd_noalloc_max_scratch_bytes() (32 MiB);
+ *   - the first call on a device resolves the array's address and configures the kernel: make it at
+ *     start-up, before any stream capture;
+ *   - every call on a device reuses the same array, which still holds the previous call's data; what must
+ *     be zero is cleared on `stream` at the start of each call.  Calls whose GPU work may overlap (other
+ *     streams, other threads) race on it -- serialise them. */
+unsigned long long b200_attn_bwd_noalloc_max_scratch_bytes(void);
+int b200_attn_bwd_noalloc(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                          void* dqkv_bf16, int batch, int seq, int heads, float dropout_p,
+                          const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+
 /* ---------------------------------------------------------------- LM head loss -------------- */
 /* Fused softmax cross-entropy forward+backward over a chunk of logits (reference gpt.py:449-453).
  * logits: bf16 [rows, ld] (ld >= vocab, padded columns ignored); labels: int64 [rows], <0 = ignore.
