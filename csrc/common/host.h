@@ -35,6 +35,9 @@ int sm_count();
 // box = {box_inner, box_rows}; 128-byte swizzle (box_inner must be 64 bf16).
 int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64_t rows, uint64_t ld,
                       uint32_t box_inner, uint32_t box_rows);
+// 128B-swizzled box of 128 bytes per row: 64 bf16 (elem_bytes 2) or 32 fp32 (elem_bytes 4) wide.
+int make_tmap_2d_sw128(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t rows, uint64_t ld,
+                       uint32_t box_rows);
 // Same without swizzle (plain row-major box), any 2-byte or 4-byte element.
 int make_tmap_2d_plain(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t rows, uint64_t ld,
                        uint32_t box_inner, uint32_t box_rows);

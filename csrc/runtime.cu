@@ -77,6 +77,13 @@ int make_tmap_2d_bf16(CUtensorMap* out, const void* base, uint64_t inner, uint64
                    CU_TENSOR_MAP_SWIZZLE_128B);
 }
 
+int make_tmap_2d_sw128(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t rows, uint64_t ld,
+                       uint32_t box_rows) {
+  B200_REQUIRE(elem_bytes == 2 || elem_bytes == 4, "sw128 tensor map: element size must be 2 or 4 bytes");
+  CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;
+  return encode_2d(out, dt, elem_bytes, base, inner, rows, ld, 128 / elem_bytes, box_rows, CU_TENSOR_MAP_SWIZZLE_128B);
+}
+
 int make_tmap_2d_plain(CUtensorMap* out, const void* base, int elem_bytes, uint64_t inner, uint64_t rows, uint64_t ld,
                        uint32_t box_inner, uint32_t box_rows) {
   CUtensorMapDataType dt = elem_bytes == 2 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT32;

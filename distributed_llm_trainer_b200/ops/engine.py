@@ -92,6 +92,7 @@ class _Workspace:
             self.dxn = torch.empty(M, h, dtype=bf, device=dev)
             self.dattn = torch.empty(M, h, dtype=bf, device=dev)
             self.dgu = torch.empty(M, 2 * I, dtype=bf, device=dev)
+            self.dact = torch.empty(M, I, dtype=bf, device=dev)
             self.dqkv = torch.empty(M, 3 * h, dtype=bf, device=dev)
             self.delta = torch.empty(B, H, S, dtype=f32, device=dev)
             self.dq_acc = torch.empty(M, h, dtype=f32, device=dev)
@@ -125,6 +126,9 @@ class FusedGPTEngine:
         self.rng_state = torch.tensor([seed & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=self.device)
         self._ws: Dict[Tuple[int, int, bool], _Workspace] = {}
         self.use_graphs = True
+        # epilogue-fusion switches (A/B-able; see profiles/): the SwiGLU' epilogue is currently slower than
+        # GEMM + streaming kernel because its per-thread-row global loads are not coalesced
+        self.fuse_swiglu_bwd = False
         self.max_ctas = 0            # cap for GEMM grids when a comm kernel needs resident SMs
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         # hooks used by the DDP / FSDP engines
@@ -222,7 +226,12 @@ class FusedGPTEngine:
         # ---- MLP branch: x_out = xmid + dropout(down(act))
         K.dropout_bwd_cast(ws.dx, ws.dy, cfg.dropout, rng, 8 * l + 2)
         self._wgrad(ws.dy, a.act, G.wd)
-        K.gemm(ws.dy, W.wd, ws.dgu, b_mn=True, epilogue=K.EPI_SWIGLU_BWD, aux=a.gu, half_n=I, N=I, max_ctas=mc)
+        if self.fuse_swiglu_bwd:
+            K.gemm(ws.dy, W.wd, ws.dgu, b_mn=True, epilogue=K.EPI_SWIGLU_BWD, aux=a.gu, half_n=I, N=I, max_ctas=mc)
+        else:
+            # d_act reuses the (dead by now) act buffer of this layer; SwiGLU' as a separate streaming kernel
+            K.gemm(ws.dy, W.wd, ws.dact, b_mn=True, max_ctas=mc)
+            K.swiglu_bwd(ws.dact, a.gu, ws.dgu)
         self._wgrad(ws.dgu, a.xn2, G.wgu)
         K.gemm(ws.dgu, W.wgu, ws.dxn, b_mn=True, max_ctas=mc)
         K.rmsnorm_bwd(ws.dxn, a.xmid, W.ln2, a.rstd2, ws.dx, G.ln2)

@@ -17,6 +17,8 @@ EPI_BF16, EPI_F32, EPI_F32_ATOMIC, EPI_ROPE_BF16, EPI_RESID_DROPOUT, EPI_SWIGLU,
 
 # launch counter: bench.py reports how many of OUR kernels ran inside the timed region
 launch_count = 0
+# route plain / fp32-accumulate GEMMs to the CTA-pair kernel (set False to A/B against the 1-CTA kernel)
+use_pair_kernel = True
 
 
 class GemmArgs(C.Structure):
@@ -35,6 +37,7 @@ class GemmArgs(C.Structure):
 _P, _I, _F, _LL, _U = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint
 _SIGS = {
     "b200_gemm_bf16": [C.POINTER(GemmArgs), _P],
+    "b200_gemm2_bf16": [C.POINTER(GemmArgs), _P],
     "b200_embed_fwd": [_P, _P, _P, _I, _I, _I, _P],
     "b200_embed_bwd": [_P, _P, _P, _I, _I, _I, _P],
     "b200_rmsnorm_fwd": [_P, _P, _P, _P, _I, _I, _F, _P],
@@ -95,8 +98,10 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
          epilogue: int = EPI_BF16, split_k: int = 1, tile_n: int = 0, max_ctas: int = 0,
          rope_cos=None, rope_sin=None, seq_len: int = 0, rope_cols: int = 0,
          residual=None, dropout_p: float = 0.0, rng_state=None, rng_stream: int = 0,
-         aux=None, half_n: int = 0, M: Optional[int] = None, N: Optional[int] = None, K: Optional[int] = None) -> None:
-    """``c = a @ b`` on tcgen05.
+         aux=None, half_n: int = 0, M: Optional[int] = None, N: Optional[int] = None, K: Optional[int] = None,
+         pair: Optional[bool] = None) -> None:
+    """``c = a @ b`` on tcgen05.  ``pair=True`` selects the CTA-pair kernel (``cta_group::2``, 256x256 tiles,
+    TMA-store epilogue); ``None`` lets ``use_pair_kernel`` decide for the epilogues that kernel implements.
 
     ``a``: K-major ``[M, K]`` or (``a_mn``) MN-major ``[K, M]``; ``b``: K-major ``[N, K]`` or (``b_mn``)
     MN-major ``[K, N]``.  Row-major 2-D tensors with unit inner stride; leading dimensions come from
@@ -117,7 +122,9 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
         residual=_ptr(residual), dropout_p=dropout_p, rng_state=_ptr(rng_state), rng_stream=rng_stream,
         aux=_ptr(aux), ld_aux=0 if aux is None else aux.stride(0), half_n=half_n,
     )
-    _call("b200_gemm_bf16", C.byref(args), _stream())
+    if pair is None:
+        pair = use_pair_kernel and epilogue <= EPI_F32_ATOMIC and N >= 256 and M >= 256
+    _call("b200_gemm2_bf16" if pair else "b200_gemm_bf16", C.byref(args), _stream())
 
 
 # ----------------------------------------------------------------------------------------------- elementwise

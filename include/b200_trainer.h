@@ -75,6 +75,11 @@ typedef struct b200_gemm_args {
 /* Reference ops G3/G6/G8/G9 (gpt.py:185-187,239,278-281,447) and their backward GEMMs. */
 int b200_gemm_bf16(const b200_gemm_args* args, void* stream);
 
+/* CTA-pair variant: tcgen05.mma.cta_group::2 over 256x256 pair tiles (each CTA stages its A rows and half of
+ * B), epilogue through swizzled smem + TMA store / TMA reduce-add.  Epilogues B200_EPI_BF16, _F32,
+ * _F32_ATOMIC; C row pitch must be a multiple of 16 bytes.  Same reference ops as b200_gemm_bf16. */
+int b200_gemm2_bf16(const b200_gemm_args* args, void* stream);
+
 /* ---------------------------------------------------------------- normalisation / elementwise */
 /* Token embedding gather into the fp32 residual stream (reference gpt.py:438). ids: int64 [rows]. */
 int b200_embed_fwd(const int64_t* ids, const void* weight_bf16, float* out, int rows, int hidden, int vocab,

@@ -1,0 +1,71 @@
+"""CTA-pair (cta_group::2) GEMM vs a PyTorch fp32 reference: all operand layouts, ragged shapes,
+fp32 store and TMA reduce-add accumulation with split-K."""
+import math
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _mk(shape, scale=1.0):
+    return (torch.randn(*shape, device="cuda") * scale).to(torch.bfloat16)
+
+
+def _ref(a, b, a_mn, b_mn):
+    A = a.float().t() if a_mn else a.float()
+    B = b.float() if b_mn else b.float().t()
+    return A @ B
+
+
+def _check(out, ref, K, what):
+    err = (out.float() - ref).abs().max().item()
+    tol = 0.02 * math.sqrt(K) + 0.05 * ref.abs().max().item() * 2 ** -7
+    assert err <= tol, f"{what}: max err {err:.4f} > {tol:.4f}"
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("M,N,K", [(256, 256, 128), (512, 768, 320), (1000, 2304, 768), (8192, 768, 256)])
+def test_gemm2_layouts(a_mn, b_mn, M, N, K):
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    torch.manual_seed(0)
+    a = _mk((K, M) if a_mn else (M, K))
+    b = _mk((K, N) if b_mn else (N, K))
+    c = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+    k.gemm(a, b, c, a_mn=a_mn, b_mn=b_mn, pair=True)
+    torch.cuda.synchronize()
+    _check(c, _ref(a, b, a_mn, b_mn), K, f"pair a_mn={a_mn} b_mn={b_mn} {M}x{N}x{K}")
+
+
+def test_gemm2_f32_and_reduce_add_splitk():
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    torch.manual_seed(2)
+    M, N, K = 768, 3072, 4096
+    a, b = _mk((K, M)), _mk((K, N))
+    ref = _ref(a, b, True, True)
+    c = torch.full((M, N), float("nan"), device="cuda")
+    k.gemm(a, b, c, a_mn=True, b_mn=True, epilogue=k.EPI_F32, pair=True)
+    torch.cuda.synchronize()
+    _check(c, ref, K, "pair f32")
+    acc = torch.ones(M, N, device="cuda")
+    k.gemm(a, b, acc, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, split_k=4, pair=True)
+    k.gemm(a, b, acc, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, pair=True)
+    torch.cuda.synchronize()
+    _check(acc, 2 * ref + 1, 2 * K, "pair reduce-add split-k")
+
+
+def test_gemm2_vocab_like_ragged_m_and_padded_ld():
+    """dW of the tied embedding: M = 50257 (ragged rows, MN-major A with a padded leading dimension)."""
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    torch.manual_seed(3)
+    V, Vp, rows, h = 5003, 5120, 384, 256
+    dlogits = torch.zeros(rows, Vp, device="cuda", dtype=torch.bfloat16)
+    dlogits[:, :V] = _mk((rows, V), 0.1)
+    x = _mk((rows, h))
+    g = torch.zeros(V, h, device="cuda")
+    k.gemm(dlogits, x, g, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, M=V, K=rows, pair=True)
+    torch.cuda.synchronize()
+    _check(g, dlogits[:, :V].float().t() @ x.float(), rows, "pair dW ragged")
