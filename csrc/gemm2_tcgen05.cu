@@ -1,4 +1,4 @@
-// bf16 GEMM, CTA-pair edition: tcgen05.mma.cta_group::2 over a 256 x 256 output tile shared by the two
+// bf16 GEMM, CTA-pair edition: tcgen05.mma.cta_group::2 over a 256 x BNP output tile shared by the two
 // CTAs of a 2-CTA cluster (one TPC).  Each CTA stages its own 128 rows of A and *half* of the B tile, so a
 // 128 x 256 slice of output costs 32 KB of operand fill per K-block instead of the 48 KB of the single-CTA
 // kernel (gemm_tcgen05.cu) -- the fix for the L2->SM fill bandwidth that bounds the small-K GEMMs of the
@@ -8,58 +8,90 @@
 //               leader CTA's full barrier (cp.async.bulk.tensor ... .cta_group::2)
 //   warp 1      TMEM allocation (both CTAs, cta_group::2); MMA issue by one thread of the LEADER CTA only;
 //               tcgen05.commit multicasts "slot free" / "accumulator ready" to both CTAs
-//   warps 2..5  epilogue (both CTAs): TMEM -> registers -> 128B-swizzled smem staging -> TMA store
-//               (cp.async.bulk.tensor), or TMA reduce-add (cp.reduce.async.bulk.tensor .add.f32) for the
-//               fp32 gradient accumulation -- coalesced full-line writes, no per-thread atomics, rows/columns
-//               beyond M/N clipped by the tensor map.
+//   warps 2..5  epilogue (both CTAs): TMEM -> registers -> fused math -> 128B-swizzled smem staging ring ->
+//               TMA store (or TMA reduce-add for fp32 gradient accumulation).  Epilogue *inputs* (fp32
+//               residual, saved gate|up) are prefetched into the same ring by TMA loads, so every global
+//               access of the epilogue is a full-line bulk transfer and rows/columns beyond M/N are clipped by
+//               the tensor maps.
 //
-// Same operand-layout freedom as the 1-CTA kernel (K-major / MN-major A and B), same b200_gemm_args.
-// Reference ops: G3/G6/G8/G9 and their dgrad/wgrad (gpt.py:185-187,239,278-281,447), cuBLASLt there.
+// Epilogues: BF16, F32, F32_ATOMIC (TMA reduce-add), ROPE_BF16, RESID_DROPOUT, SWIGLU, SWIGLU_BWD -- the same
+// set and the same b200_gemm_args as the single-CTA kernel; see that file / the header for the math.
+// Reference ops: G3/G4/G6/G7/G8/G9 and their dgrad/wgrad (gpt.py:116-147,185-187,239-240,278-282,447).
 #include <cuda_bf16.h>
 
 #include "../include/b200_trainer.h"
 #include "common/host.h"
+#include "common/philox.cuh"
 #include "common/ptx.cuh"
 
 namespace b200 {
 namespace g2 {
 
-constexpr int BM = 128;        // rows per CTA (256 per pair)
-constexpr int BNP = 256;       // tile width of the pair
-constexpr int BNH = 128;       // B rows staged per CTA
+constexpr int BM = 128;   // rows per CTA (256 per pair)
 constexpr int BK = 64;
 constexpr int UMMA_K = 16;
-constexpr int kAStage = BM * BK * 2;    // 16 KB
-constexpr int kBStage = BNH * BK * 2;   // 16 KB
-constexpr int kStage = kAStage + kBStage;
-constexpr int kStages = 5;
-constexpr int kEpiBufs = 4;
-constexpr int kEpiBuf = 128 * 128;      // 128 rows x 128 B
-constexpr int kBarOff = kStages * kStage + kEpiBufs * kEpiBuf;
-constexpr int kSmemTotal = kBarOff + 256 + 1024;
+constexpr int kAStage = BM * BK * 2;   // 16 KB
+constexpr int kEpiBuf = 128 * 128;     // staging slot: 128 rows x 128 B
 
-enum { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2 };
+enum {
+  EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2, EPI_ROPE_BF16 = 3, EPI_RESID_DROPOUT = 4, EPI_SWIGLU = 5,
+  EPI_SWIGLU_BWD = 6
+};
+
+template <int BNP, int EPI>
+struct Cfg {
+  static constexpr int BNH = BNP / 2;                       // B rows staged per CTA
+  static constexpr int kBStage = BNH * BK * 2;
+  static constexpr int kStage = kAStage + kBStage;
+  static constexpr int kEpiBufs = (EPI == EPI_SWIGLU_BWD) ? 6 : 4;
+  static constexpr int kStages = (EPI == EPI_SWIGLU_BWD) ? 4 : (BNP == 256 ? 5 : 6);
+  static constexpr int kEpiOff = kStages * kStage;
+  static constexpr int kBarOff = kEpiOff + kEpiBufs * kEpiBuf;
+  static constexpr int kSmemTotal = kBarOff + 256 + 1024;
+  static constexpr uint32_t kTmemCols = 2 * BNP;             // double-buffered accumulator
+  static_assert(kSmemTotal <= 232448, "shared memory budget exceeded");
+};
 
 struct Params {
   int M, N, K;
   int split_k, k_per_split;
+  const float* rope_cos;
+  const float* rope_sin;
+  int seq_len, rope_cols;
+  float dropout_p;
+  const unsigned long long* rng;
+  unsigned int rng_stream;
+  int half_n;
 };
 
-template <bool A_MN, bool B_MN, int EPI>
+__device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
+  return v;
+}
+__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+
+// tma_c: primary output.  tma_x: second tensor -- RESID_DROPOUT: residual (fp32, input); SWIGLU: act (bf16,
+// output); SWIGLU_BWD: saved [gate|up] (bf16, input).
+template <int BNP, bool A_MN, bool B_MN, int EPI>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-             const __grid_constant__ CUtensorMap tma_c, const Params p) {
+             const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p) {
+  using C = Cfg<BNP, EPI>;
+  constexpr int kStages = C::kStages;
+  constexpr int NB = C::kEpiBufs;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
   uint8_t* smem_b = smem + kStages * kAStage;
-  uint8_t* smem_epi = smem + kStages * kStage;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + kBarOff);
-  uint64_t* full_bar = bars;                      // [kStages]  (leader's copy is the one that is waited on)
-  uint64_t* empty_bar = bars + kStages;           // [kStages]  (per CTA, signalled by multicast commit)
-  uint64_t* tmem_full = bars + 2 * kStages;       // [2]        (per CTA, multicast commit)
-  uint64_t* tmem_empty = bars + 2 * kStages + 2;  // [2]        (leader's copy: 8 epilogue warps arrive)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 4);
+  uint8_t* smem_epi = smem + C::kEpiOff;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + C::kBarOff);
+  uint64_t* full_bar = bars;                      // [kStages]  leader's copy is waited on
+  uint64_t* empty_bar = bars + kStages;           // [kStages]  per CTA, multicast commit
+  uint64_t* tmem_full = bars + 2 * kStages;       // [2]        per CTA, multicast commit
+  uint64_t* tmem_empty = bars + 2 * kStages + 2;  // [2]        leader's copy: 8 epilogue warps arrive
+  uint64_t* ld_bar = bars + 2 * kStages + 4;      // [6]        epilogue input loads (per CTA)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 2 * kStages + 10);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta_rank = cluster_ctarank();
@@ -68,13 +100,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
 
   const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int tiles_n = (p.N + BNP - 1) / BNP;
-  const int num_tiles = tiles_m * tiles_n * p.split_k;
+  const int tiles_mn = tiles_m * tiles_n;
+  const int num_tiles = tiles_mn * p.split_k;
   const int k_blocks_total = (p.K + BK - 1) / BK;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tma_a);
     tma_prefetch_desc(&tma_b);
     tma_prefetch_desc(&tma_c);
+    if constexpr (EPI >= EPI_RESID_DROPOUT) tma_prefetch_desc(&tma_x);
     for (int i = 0; i < kStages; ++i) {
       mbar_init(&full_bar[i], 1);
       mbar_init(&empty_bar[i], 1);
@@ -83,10 +117,11 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       mbar_init(&tmem_full[i], 1);
       mbar_init(&tmem_empty[i], 8);
     }
+    for (int i = 0; i < 6; ++i) mbar_init(&ld_bar[i], 1);
     fence_barrier_init();
   }
   cluster_sync_all();   // barrier inits visible to the peer before any remote arrive / multicast commit
-  if (warp == 1) tmem_alloc_cg2<512>(tmem_ptr);
+  if (warp == 1) tmem_alloc_cg2<C::kTmemCols>(tmem_ptr);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -98,17 +133,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       int stage = 0;
       uint32_t phase = 0;
       for (int t = pair; t < num_tiles; t += npairs) {
-        const int ks = t / (tiles_m * tiles_n);
-        const int r = t - ks * tiles_m * tiles_n;
+        const int ks = t / tiles_mn;
+        const int r = t - ks * tiles_mn;
         const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;   // this CTA's rows
-        const int n0 = (r / tiles_m) * BNP + int(cta_rank) * BNH;     // this CTA's half of the B tile
+        const int nt = (r / tiles_m) * BNP;
+        // this CTA's half of the B tile; SwiGLU: leader stages gate rows, peer the matching up rows
+        const int n0 = (EPI == EPI_SWIGLU) ? (cta_rank == 0 ? nt / 2 : p.half_n + nt / 2) : nt + int(cta_rank) * C::BNH;
         const int kb0 = ks * p.k_per_split;
         const int kb1 = min(k_blocks_total, kb0 + p.k_per_split);
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
-          if (leader) mbar_expect_tx(&full_bar[stage], 2 * kStage);   // bytes of both CTAs land on this barrier
+          if (leader) mbar_expect_tx(&full_bar[stage], 2 * C::kStage);   // bytes of both CTAs land on this barrier
           uint8_t* sa = smem_a + stage * kAStage;
-          uint8_t* sb = smem_b + stage * kBStage;
+          uint8_t* sb = smem_b + stage * C::kBStage;
           const int k0 = kb * BK;
           if constexpr (!A_MN) {
             tma_load_2d_cg2(sa, &tma_a, &full_bar[stage], k0, m0);
@@ -120,7 +157,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             tma_load_2d_cg2(sb, &tma_b, &full_bar[stage], k0, n0);
           } else {
 #pragma unroll
-            for (int c = 0; c < BNH / 64; ++c) tma_load_2d_cg2(sb + c * (BK * 128), &tma_b, &full_bar[stage], n0 + c * 64, k0);
+            for (int c = 0; c < C::BNH / 64; ++c) tma_load_2d_cg2(sb + c * (BK * 128), &tma_b, &full_bar[stage], n0 + c * 64, k0);
           }
           if (++stage == kStages) { stage = 0; phase ^= 1; }
         }
@@ -134,7 +171,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       uint32_t phase = 0;
       int it = 0;
       for (int t = pair; t < num_tiles; t += npairs, ++it) {
-        const int ks = t / (tiles_m * tiles_n);
+        const int ks = t / tiles_mn;
         const int kb0 = ks * p.k_per_split;
         const int kb1 = min(k_blocks_total, kb0 + p.k_per_split);
         const int buf = it & 1;
@@ -146,7 +183,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           mbar_wait(&full_bar[stage], phase);
           tc_fence_after();
           const uint32_t a_addr = smem_u32(smem_a + stage * kAStage);
-          const uint32_t b_addr = smem_u32(smem_b + stage * kBStage);
+          const uint32_t b_addr = smem_u32(smem_b + stage * C::kBStage);
 #pragma unroll
           for (int j = 0; j < BK / UMMA_K; ++j) {
             const uint64_t da = A_MN ? make_smem_desc_sw128(a_addr + j * (UMMA_K * 128), BK * 128, 1024)
@@ -164,69 +201,279 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   } else {
     // ------------------------------------------------------------------ epilogue warps (both CTAs)
     const int q = warp & 3;
-    const int r_in = q * 32 + lane;                       // row within this CTA's 128 x 256 accumulator
+    const int r_in = q * 32 + lane;                       // row within this CTA's 128 x BNP accumulator
+    const int sw = r_in & 7;
     const bool epi_leader = threadIdx.x == 64;
-    constexpr int kChunkCols = (EPI == EPI_BF16) ? 64 : 32;   // 128 bytes per row per staging buffer
-    constexpr int kChunks = BNP / kChunkCols;
-    uint32_t g = 0;                                       // running chunk counter -> staging ring slot
-    int it = 0;
-    for (int t = pair; t < num_tiles; t += npairs, ++it) {
-      const int ks = t / (tiles_m * tiles_n);
-      const int r = t - ks * tiles_m * tiles_n;
+    const uint32_t lane_off = uint32_t(q * 32) << 16;
+    const uint32_t epi_base = smem_u32(smem_epi);
+    const int my_tiles = (num_tiles - pair + npairs - 1) / npairs;   // tiles this pair processes (>= 0)
+
+    // "unit" = the amount of output handled per staging step; units are numbered across tiles so that the
+    // staging ring and the input prefetch run ahead over tile boundaries.
+    constexpr int kUnitCols = (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC || EPI == EPI_RESID_DROPOUT) ? 32 : 64;
+    constexpr int kUnits = (EPI == EPI_SWIGLU) ? BNP / 128 : BNP / kUnitCols;   // per tile
+    const long total_units = (long)my_tiles * kUnits;
+    auto unit_coords = [&](long u, int& m0, int& n0, int& c) {
+      const int it = int(u / kUnits);
+      c = int(u - (long)it * kUnits);
+      const int t = pair + it * npairs;
+      const int r = t % tiles_mn;
+      m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
+      n0 = (r / tiles_m) * BNP;
+    };
+    // store-only staging step: slot g % NB
+    uint32_t g = 0;
+    auto stage_begin = [&]() -> uint32_t {
+      if (epi_leader) tma_store_wait_read<NB - 1>();   // the store that last read this slot is done with it
+      named_bar_sync(1, 128);
+      return epi_base + (g % NB) * kEpiBuf;
+    };
+    auto stage_end = [&](const CUtensorMap* map, int col, int row, bool reduce) {
+      fence_proxy_async_smem();
+      named_bar_sync(1, 128);
+      if (epi_leader) {
+        if (reduce) tma_reduce_add_2d(map, smem_epi + (g % NB) * kEpiBuf, col, row);
+        else tma_store_2d(map, smem_epi + (g % NB) * kEpiBuf, col, row);
+        tma_store_commit();
+      }
+      ++g;
+    };
+    auto put_bf16x64 = [&](uint32_t slot, const uint32_t* v0, const uint32_t* v1) {   // fp32 bits -> bf16 row
+      const uint32_t row_addr = slot + r_in * 128;
+#pragma unroll
+      for (int cc = 0; cc < 8; ++cc) {
+        const uint32_t* v = cc < 4 ? v0 + cc * 8 : v1 + (cc - 4) * 8;
+        st_shared_v4_u32(row_addr + ((cc ^ sw) << 4), pack_bf16x2(__uint_as_float(v[0]), __uint_as_float(v[1])),
+                         pack_bf16x2(__uint_as_float(v[2]), __uint_as_float(v[3])),
+                         pack_bf16x2(__uint_as_float(v[4]), __uint_as_float(v[5])),
+                         pack_bf16x2(__uint_as_float(v[6]), __uint_as_float(v[7])));
+      }
+    };
+    auto release_tmem = [&](int buf) {
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_leader(&tmem_empty[buf]);
+    };
+
+    if constexpr (EPI == EPI_RESID_DROPOUT) {
+      // prefetch the residual two units ahead into the slot that unit will also be stored from
+      auto issue_load = [&](long u) {
+        if (u < total_units) {
+          int m0, n0, c;
+          unit_coords(u, m0, n0, c);
+          mbar_expect_tx(&ld_bar[u % NB], kEpiBuf);
+          tma_load_2d(smem_epi + (u % NB) * kEpiBuf, &tma_x, &ld_bar[u % NB], n0 + c * 32, m0);
+        }
+      };
+      if (epi_leader) { issue_load(0); issue_load(1); }
+    }
+    if constexpr (EPI == EPI_SWIGLU_BWD) {
+      auto issue_load = [&](long u) {
+        if (u < total_units) {
+          int m0, n0, c;
+          unit_coords(u, m0, n0, c);
+          const int pr = int(u % 3);
+          mbar_expect_tx(&ld_bar[pr], 2 * kEpiBuf);
+          tma_load_2d(smem_epi + (2 * pr) * kEpiBuf, &tma_x, &ld_bar[pr], n0 + c * 64, m0);
+          tma_load_2d(smem_epi + (2 * pr + 1) * kEpiBuf, &tma_x, &ld_bar[pr], p.half_n + n0 + c * 64, m0);
+        }
+      };
+      if (epi_leader) issue_load(0);
+    }
+
+    const bool drop = p.dropout_p > 0.f;
+    const uint32_t thresh = dropout_threshold16(p.dropout_p);
+    const float inv_keep = drop ? 1.0f / (1.0f - p.dropout_p) : 1.0f;
+    unsigned long long seed = 0, offs = 0;
+    if (EPI == EPI_RESID_DROPOUT && drop) { seed = p.rng[0]; offs = p.rng[1]; }
+
+    long u_glob = 0;
+    for (int it = 0; it < my_tiles; ++it) {
+      const int t = pair + it * npairs;
+      const int r = t % tiles_mn;
       const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
       const int n0 = (r / tiles_m) * BNP;
+      const int row = m0 + r_in;
       const int buf = it & 1;
       const uint32_t buf_phase = (it >> 1) & 1;
-      (void)ks;
       mbar_wait(&tmem_full[buf], buf_phase);
       tc_fence_after();
-      const uint32_t t_row = tmem_base + (uint32_t(q * 32) << 16) + buf * BNP;
+      const uint32_t t_row = tmem_base + lane_off + buf * BNP;
+
+      if constexpr (EPI == EPI_BF16 || EPI == EPI_ROPE_BF16) {
 #pragma unroll 1
-      for (int c = 0; c < kChunks; ++c, ++g) {
-        const uint32_t slot = smem_u32(smem_epi + (g % kEpiBufs) * kEpiBuf);
-        // the TMA store that last read this slot (kEpiBufs chunks ago) must be done with it
-        if (epi_leader) tma_store_wait_read<kEpiBufs - 1>();
-        named_bar_sync(1, 128);
-        const uint32_t row_addr = slot + r_in * 128;
-        if constexpr (EPI == EPI_BF16) {
+        for (int c = 0; c < kUnits; ++c) {
+          const uint32_t slot = stage_begin();
           uint32_t v0[32], v1[32];
           tmem_ld_32x32b_x32(t_row + c * 64, v0);
           tmem_ld_32x32b_x32(t_row + c * 64 + 32, v1);
           tmem_ld_wait();
+          if (c == kUnits - 1) release_tmem(buf);
+          if constexpr (EPI == EPI_ROPE_BF16) {
+            if (n0 + c * 64 < p.rope_cols) {   // one 64-column unit = one head; column j pairs with j + 32
+              const int pos = (row < p.M ? row : 0) % p.seq_len;
+              const float4* cs = reinterpret_cast<const float4*>(p.rope_cos + size_t(pos) * 32);
+              const float4* sn = reinterpret_cast<const float4*>(p.rope_sin + size_t(pos) * 32);
 #pragma unroll
-          for (int cc = 0; cc < 4; ++cc)
-            st_shared_v4_u32(row_addr + ((cc ^ (r_in & 7)) << 4),
-                             pack_bf16x2(__uint_as_float(v0[cc * 8 + 0]), __uint_as_float(v0[cc * 8 + 1])),
-                             pack_bf16x2(__uint_as_float(v0[cc * 8 + 2]), __uint_as_float(v0[cc * 8 + 3])),
-                             pack_bf16x2(__uint_as_float(v0[cc * 8 + 4]), __uint_as_float(v0[cc * 8 + 5])),
-                             pack_bf16x2(__uint_as_float(v0[cc * 8 + 6]), __uint_as_float(v0[cc * 8 + 7])));
+              for (int g4 = 0; g4 < 8; ++g4) {
+                const float4 cc = cs[g4], ss = sn[g4];
+                const float cv[4] = {cc.x, cc.y, cc.z, cc.w}, sv[4] = {ss.x, ss.y, ss.z, ss.w};
 #pragma unroll
-          for (int cc = 0; cc < 4; ++cc)
-            st_shared_v4_u32(row_addr + (((cc + 4) ^ (r_in & 7)) << 4),
-                             pack_bf16x2(__uint_as_float(v1[cc * 8 + 0]), __uint_as_float(v1[cc * 8 + 1])),
-                             pack_bf16x2(__uint_as_float(v1[cc * 8 + 2]), __uint_as_float(v1[cc * 8 + 3])),
-                             pack_bf16x2(__uint_as_float(v1[cc * 8 + 4]), __uint_as_float(v1[cc * 8 + 5])),
-                             pack_bf16x2(__uint_as_float(v1[cc * 8 + 6]), __uint_as_float(v1[cc * 8 + 7])));
-        } else {
+                for (int e = 0; e < 4; ++e) {
+                  const float x1 = __uint_as_float(v0[g4 * 4 + e]), x2 = __uint_as_float(v1[g4 * 4 + e]);
+                  v0[g4 * 4 + e] = __float_as_uint(x1 * cv[e] - x2 * sv[e]);
+                  v1[g4 * 4 + e] = __float_as_uint(x2 * cv[e] + x1 * sv[e]);
+                }
+              }
+            }
+          }
+          put_bf16x64(slot, v0, v1);
+          stage_end(&tma_c, n0 + c * 64, m0, false);
+        }
+      } else if constexpr (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC) {
+#pragma unroll 1
+        for (int c = 0; c < kUnits; ++c) {
+          const uint32_t slot = stage_begin();
           uint32_t v[32];
           tmem_ld_32x32b_x32(t_row + c * 32, v);
           tmem_ld_wait();
+          if (c == kUnits - 1) release_tmem(buf);
+          const uint32_t row_addr = slot + r_in * 128;
 #pragma unroll
           for (int cc = 0; cc < 8; ++cc)
-            st_shared_v4_u32(row_addr + ((cc ^ (r_in & 7)) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
+            st_shared_v4_u32(row_addr + ((cc ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
+          stage_end(&tma_c, n0 + c * 32, m0, EPI == EPI_F32_ATOMIC);
         }
-        if (c == kChunks - 1) {
-          // accumulator fully read: hand the TMEM buffer back to the MMA thread of the leader CTA
-          tc_fence_before();
-          __syncwarp();
-          if (lane == 0) mbar_arrive_leader(&tmem_empty[buf]);
+      } else if constexpr (EPI == EPI_RESID_DROPOUT) {
+#pragma unroll 1
+        for (int c = 0; c < kUnits; ++c, ++u_glob) {
+          // keep the residual prefetch two units ahead; its slot was last read by the store of unit u-2
+          if (epi_leader) {
+            tma_store_wait_read<1>();
+            const long un = u_glob + 2;
+            if (un < total_units) {
+              int pm0, pn0, pc;
+              unit_coords(un, pm0, pn0, pc);
+              mbar_expect_tx(&ld_bar[un % NB], kEpiBuf);
+              tma_load_2d(smem_epi + (un % NB) * kEpiBuf, &tma_x, &ld_bar[un % NB], pn0 + pc * 32, pm0);
+            }
+          }
+          const uint32_t slot = epi_base + uint32_t(u_glob % NB) * kEpiBuf;
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_row + c * 32, v);
+          tmem_ld_wait();
+          if (c == kUnits - 1) release_tmem(buf);
+          mbar_wait(&ld_bar[u_glob % NB], uint32_t(u_glob / NB) & 1);
+          const uint32_t row_addr = slot + r_in * 128;
+          const int col0 = n0 + c * 32;
+#pragma unroll
+          for (int g8 = 0; g8 < 4; ++g8) {
+            uint32_t keep = 0xFF;
+            if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + g8), thresh);
+#pragma unroll
+            for (int hlf = 0; hlf < 2; ++hlf) {
+              const int cc = g8 * 2 + hlf;
+              const uint32_t addr = row_addr + ((cc ^ sw) << 4);
+              const uint4 rq = ld_shared_v4(addr);
+              const float rr[4] = {__uint_as_float(rq.x), __uint_as_float(rq.y), __uint_as_float(rq.z), __uint_as_float(rq.w)};
+              uint32_t o[4];
+#pragma unroll
+              for (int e = 0; e < 4; ++e) {
+                const float a = ((keep >> (hlf * 4 + e)) & 1) ? __uint_as_float(v[cc * 4 + e]) * inv_keep : 0.f;
+                o[e] = __float_as_uint(rr[e] + a);
+              }
+              st_shared_v4_u32(addr, o[0], o[1], o[2], o[3]);
+            }
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (epi_leader) {
+            tma_store_2d(&tma_c, smem_epi + (u_glob % NB) * kEpiBuf, col0, m0);
+            tma_store_commit();
+          }
         }
-        fence_proxy_async_smem();
-        named_bar_sync(1, 128);
-        if (epi_leader) {
-          if constexpr (EPI == EPI_F32_ATOMIC) tma_reduce_add_2d(&tma_c, smem_epi + (g % kEpiBufs) * kEpiBuf, n0 + c * kChunkCols, m0);
-          else tma_store_2d(&tma_c, smem_epi + (g % kEpiBufs) * kEpiBuf, n0 + c * kChunkCols, m0);
-          tma_store_commit();
+      } else if constexpr (EPI == EPI_SWIGLU) {
+        // accumulator columns [0, BNP/2) = gate, [BNP/2, BNP) = up, for intermediate columns n0/2 ...
+#pragma unroll 1
+        for (int c = 0; c < kUnits; ++c) {
+          uint32_t g0[32], g1[32], u0[32], u1[32];
+          tmem_ld_32x32b_x32(t_row + c * 64, g0);
+          tmem_ld_32x32b_x32(t_row + c * 64 + 32, g1);
+          tmem_ld_32x32b_x32(t_row + BNP / 2 + c * 64, u0);
+          tmem_ld_32x32b_x32(t_row + BNP / 2 + c * 64 + 32, u1);
+          tmem_ld_wait();
+          if (c == kUnits - 1) release_tmem(buf);
+          const int icol = n0 / 2 + c * 64;   // intermediate column
+          uint32_t slot = stage_begin();
+          put_bf16x64(slot, g0, g1);
+          stage_end(&tma_c, icol, m0, false);
+          slot = stage_begin();
+          put_bf16x64(slot, u0, u1);
+          stage_end(&tma_c, p.half_n + icol, m0, false);
+          // activation from the bf16-rounded gate / up so that backward recomputation is bit-identical
+#pragma unroll
+          for (int e = 0; e < 32; ++e) {
+            const float ga = __bfloat162float(__float2bfloat16_rn(__uint_as_float(g0[e])));
+            const float ua = __bfloat162float(__float2bfloat16_rn(__uint_as_float(u0[e])));
+            const float gb = __bfloat162float(__float2bfloat16_rn(__uint_as_float(g1[e])));
+            const float ub = __bfloat162float(__float2bfloat16_rn(__uint_as_float(u1[e])));
+            g0[e] = __float_as_uint(ga * sigmoid_f(ga) * ua);
+            g1[e] = __float_as_uint(gb * sigmoid_f(gb) * ub);
+          }
+          slot = stage_begin();
+          put_bf16x64(slot, g0, g1);
+          stage_end(&tma_x, icol, m0, false);
+        }
+      } else {  // EPI_SWIGLU_BWD: acc = d_act; inputs gate/up via TMA; outputs [dgate | dup]
+#pragma unroll 1
+        for (int c = 0; c < kUnits; ++c, ++u_glob) {
+          const int pr = int(u_glob % 3);
+          if (epi_leader) {
+            // the pair of slots unit u+1 loads into was last read by the stores of unit u-2
+            tma_store_wait_read<1>();
+            const long un = u_glob + 1;
+            if (un < total_units) {
+              int pm0, pn0, pc;
+              unit_coords(un, pm0, pn0, pc);
+              const int npr = int(un % 3);
+              mbar_expect_tx(&ld_bar[npr], 2 * kEpiBuf);
+              tma_load_2d(smem_epi + (2 * npr) * kEpiBuf, &tma_x, &ld_bar[npr], pn0 + pc * 64, pm0);
+              tma_load_2d(smem_epi + (2 * npr + 1) * kEpiBuf, &tma_x, &ld_bar[npr], p.half_n + pn0 + pc * 64, pm0);
+            }
+          }
+          uint32_t d0[32], d1[32];
+          tmem_ld_32x32b_x32(t_row + c * 64, d0);
+          tmem_ld_32x32b_x32(t_row + c * 64 + 32, d1);
+          tmem_ld_wait();
+          if (c == kUnits - 1) release_tmem(buf);
+          mbar_wait(&ld_bar[pr], uint32_t(u_glob / 3) & 1);
+          const uint32_t g_row = epi_base + (2 * pr) * kEpiBuf + r_in * 128;
+          const uint32_t u_row = g_row + kEpiBuf;
+#pragma unroll
+          for (int cc = 0; cc < 8; ++cc) {
+            const uint32_t ga = g_row + ((cc ^ sw) << 4), ua = u_row + ((cc ^ sw) << 4);
+            const uint4 gq = ld_shared_v4(ga), uq = ld_shared_v4(ua);
+            const uint32_t gw[4] = {gq.x, gq.y, gq.z, gq.w}, uw[4] = {uq.x, uq.y, uq.z, uq.w};
+            const uint32_t* d = cc < 4 ? d0 + cc * 8 : d1 + (cc - 4) * 8;
+            uint32_t og[4], ou[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float2 gg = unpack_bf16x2(gw[e]), uu = unpack_bf16x2(uw[e]);
+              const float da = __uint_as_float(d[2 * e]), db = __uint_as_float(d[2 * e + 1]);
+              const float s0 = sigmoid_f(gg.x), s1 = sigmoid_f(gg.y);
+              og[e] = pack_bf16x2(da * uu.x * s0 * (1.0f + gg.x * (1.0f - s0)), db * uu.y * s1 * (1.0f + gg.y * (1.0f - s1)));
+              ou[e] = pack_bf16x2(da * gg.x * s0, db * gg.y * s1);
+            }
+            st_shared_v4_u32(ga, og[0], og[1], og[2], og[3]);
+            st_shared_v4_u32(ua, ou[0], ou[1], ou[2], ou[3]);
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(1, 128);
+          if (epi_leader) {
+            tma_store_2d(&tma_c, smem_epi + (2 * pr) * kEpiBuf, n0 + c * 64, m0);
+            tma_store_2d(&tma_c, smem_epi + (2 * pr + 1) * kEpiBuf, p.half_n + n0 + c * 64, m0);
+            tma_store_commit();
+          }
         }
       }
     }
@@ -237,31 +484,50 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   cluster_sync_all();   // nobody exits (or frees TMEM) while the peer may still signal it
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc_cg2<512>(tmem_base);
+    tmem_dealloc_cg2<C::kTmemCols>(tmem_base);
   }
 }
 
-template <bool A_MN, bool B_MN, int EPI>
-static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const Params& p, int grid,
-                  cudaStream_t stream) {
-  auto kfn = gemm2_kernel<A_MN, B_MN, EPI>;
+template <int BNP, bool A_MN, bool B_MN, int EPI>
+static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
+                  const Params& p, int grid, cudaStream_t stream) {
+  auto kfn = gemm2_kernel<BNP, A_MN, B_MN, EPI>;
   static bool configured = false;
   if (!configured) {
-    B200_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, kSmemTotal));
+    B200_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BNP, EPI>::kSmemTotal));
     configured = true;
   }
-  kfn<<<grid, 192, kSmemTotal, stream>>>(ta, tb, tc, p);
+  kfn<<<grid, 192, Cfg<BNP, EPI>::kSmemTotal, stream>>>(ta, tb, tc, tx, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
 
-template <int EPI>
+template <int BNP, int EPI>
 static int dispatch(bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc,
-                    const Params& p, int grid, cudaStream_t s) {
-  if (!a_mn && !b_mn) return launch<false, false, EPI>(ta, tb, tc, p, grid, s);
-  if (!a_mn && b_mn) return launch<false, true, EPI>(ta, tb, tc, p, grid, s);
-  if (a_mn && b_mn) return launch<true, true, EPI>(ta, tb, tc, p, grid, s);
-  return launch<true, false, EPI>(ta, tb, tc, p, grid, s);
+                    const CUtensorMap& tx, const Params& p, int grid, cudaStream_t s) {
+  if (!a_mn && !b_mn) return launch<BNP, false, false, EPI>(ta, tb, tc, tx, p, grid, s);
+  if (!a_mn && b_mn) return launch<BNP, false, true, EPI>(ta, tb, tc, tx, p, grid, s);
+  if constexpr (EPI <= EPI_F32_ATOMIC) {
+    if (a_mn && b_mn) return launch<BNP, true, true, EPI>(ta, tb, tc, tx, p, grid, s);
+    return launch<BNP, true, false, EPI>(ta, tb, tc, tx, p, grid, s);
+  }
+  set_error("gemm2: MN-major A is not instantiated for epilogue %d", EPI);
+  return -2;
+}
+
+template <int BNP>
+static int dispatch_epi(int epi, bool a_mn, bool b_mn, const CUtensorMap& ta, const CUtensorMap& tb,
+                        const CUtensorMap& tc, const CUtensorMap& tx, const Params& p, int grid, cudaStream_t s) {
+  switch (epi) {
+    case EPI_BF16: return dispatch<BNP, EPI_BF16>(a_mn, b_mn, ta, tb, tc, tx, p, grid, s);
+    case EPI_F32: return dispatch<BNP, EPI_F32>(a_mn, b_mn, ta, tb, tc, tx, p, grid, s);
+    case EPI_F32_ATOMIC: return dispatch<BNP, EPI_F32_ATOMIC>(a_mn, b_mn, ta, tb, tc, tx, p, grid, s);
+    case EPI_ROPE_BF16: return dispatch<BNP, EPI_ROPE_BF16>(a_mn, b_mn, ta, tb, tc, tx, p, grid, s);
+    case EPI_RESID_DROPOUT: return dispatch<BNP, EPI_RESID_DROPOUT>(a_mn, b_mn, ta, tb, tc, tx, p, grid, s);
+    case EPI_SWIGLU_BWD: return dispatch<BNP, EPI_SWIGLU_BWD>(a_mn, b_mn, ta, tb, tc, tx, p, grid, s);
+  }
+  set_error("gemm2: unknown epilogue %d", epi);
+  return -2;
 }
 
 }  // namespace g2
@@ -275,21 +541,46 @@ extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) {
   B200_REQUIRE(a != nullptr, "gemm2: null args");
   B200_REQUIRE(a->M > 0 && a->N > 0 && a->K > 0, "gemm2: empty problem %dx%dx%d", a->M, a->N, a->K);
   B200_REQUIRE(a->lda % 8 == 0 && a->ldb % 8 == 0, "gemm2: lda/ldb must be multiples of 8 elements");
-  B200_REQUIRE(a->epilogue >= EPI_BF16 && a->epilogue <= EPI_F32_ATOMIC,
-               "gemm2: epilogue %d is only available in the single-CTA kernel (b200_gemm_bf16)", a->epilogue);
+  const int epi = a->epilogue;
+  B200_REQUIRE(epi >= EPI_BF16 && epi <= EPI_SWIGLU_BWD, "gemm2: unknown epilogue %d", epi);
   const bool a_mn = a->a_mn_major != 0, b_mn = a->b_mn_major != 0;
-  const int c_elem = a->epilogue == EPI_BF16 ? 2 : 4;
+  const bool c_f32 = epi == EPI_F32 || epi == EPI_F32_ATOMIC || epi == EPI_RESID_DROPOUT;
+  const int c_elem = c_f32 ? 4 : 2;
   B200_REQUIRE((size_t(a->ldc) * c_elem) % 16 == 0, "gemm2: C row pitch must be a multiple of 16 bytes");
+  if (epi == EPI_ROPE_BF16) B200_REQUIRE(a->rope_cols % 64 == 0 && a->rope_cos && a->rope_sin && a->seq_len > 0, "gemm2: bad rotary arguments");
+  if (epi == EPI_RESID_DROPOUT) {
+    B200_REQUIRE(a->residual != nullptr, "gemm2: residual required");
+    B200_REQUIRE(a->dropout_p == 0.f || a->rng_state != nullptr, "gemm2: rng_state required when dropout_p > 0");
+    B200_REQUIRE(a->N % 8 == 0, "gemm2: N %% 8 != 0");
+  }
+  if (epi == EPI_SWIGLU) B200_REQUIRE(a->N == 2 * a->half_n && a->half_n % 128 == 0 && a->aux != nullptr && !b_mn, "gemm2: SwiGLU needs N == 2*half_n, half_n %% 128 == 0, K-major B and an act output");
+  if (epi == EPI_SWIGLU_BWD) B200_REQUIRE(a->N == a->half_n && a->aux != nullptr, "gemm2: SwiGLU' needs N == half_n and the saved [gate|up]");
 
-  CUtensorMap ta, tb, tc;
+  // tile width: 256 unless the narrower pair tile fills the machine better (N = 768/1024 with few row tiles)
+  int bnp = a->tile_n == 128 ? 128 : 256;
+  if (a->tile_n != 128 && a->tile_n != 256 && epi != EPI_SWIGLU) {
+    const int pairs_hw = sm_count() / 2;
+    const int split = a->split_k > 0 ? a->split_k : 1;
+    auto waves = [&](int w) { long t = long((a->M + 255) / 256) * ((a->N + w - 1) / w) * split; return double((t + pairs_hw - 1) / pairs_hw); };
+    bnp = (waves(128) * 0.56 < waves(256)) ? 128 : 256;
+  }
+  if (epi == EPI_SWIGLU) bnp = 256;
+
+  CUtensorMap ta, tb, tc, tx;
   int rc;
   if (!a_mn) rc = make_tmap_2d_bf16(&ta, a->A, a->K, a->M, a->lda, 64, BM);
   else       rc = make_tmap_2d_bf16(&ta, a->A, a->M, a->K, a->lda, 64, BK);
   if (rc) return rc;
-  if (!b_mn) rc = make_tmap_2d_bf16(&tb, a->B, a->K, a->N, a->ldb, 64, BNH);
+  if (!b_mn) rc = make_tmap_2d_bf16(&tb, a->B, a->K, a->N, a->ldb, 64, bnp / 2);
   else       rc = make_tmap_2d_bf16(&tb, a->B, a->N, a->K, a->ldb, 64, BK);
   if (rc) return rc;
-  rc = make_tmap_2d_sw128(&tc, a->C, c_elem, a->N, a->M, a->ldc, 128);
+  const int c_cols = epi == EPI_SWIGLU_BWD ? 2 * a->half_n : a->N;   // SwiGLU': C = [dgate | dup] is 2*half_n wide
+  rc = make_tmap_2d_sw128(&tc, a->C, c_elem, c_cols, a->M, a->ldc, 128);
+  if (rc) return rc;
+  tx = tc;
+  if (epi == EPI_RESID_DROPOUT) rc = make_tmap_2d_sw128(&tx, a->residual, 4, a->N, a->M, a->ldc, 128);
+  else if (epi == EPI_SWIGLU) rc = make_tmap_2d_sw128(&tx, a->aux, 2, a->half_n, a->M, a->ld_aux, 128);
+  else if (epi == EPI_SWIGLU_BWD) rc = make_tmap_2d_sw128(&tx, a->aux, 2, 2 * a->half_n, a->M, a->ld_aux, 128);
   if (rc) return rc;
 
   Params p{};
@@ -297,20 +588,20 @@ extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) {
   const int kblocks = (a->K + BK - 1) / BK;
   int split = a->split_k > 0 ? a->split_k : 1;
   if (split > kblocks) split = kblocks;
-  if (split > 1) B200_REQUIRE(a->epilogue == EPI_F32_ATOMIC, "gemm2: split-K needs the fp32 reduce-add epilogue");
+  if (split > 1) B200_REQUIRE(epi == EPI_F32_ATOMIC, "gemm2: split-K needs the fp32 reduce-add epilogue");
   p.k_per_split = (kblocks + split - 1) / split;
   p.split_k = (kblocks + p.k_per_split - 1) / p.k_per_split;
+  p.rope_cos = a->rope_cos; p.rope_sin = a->rope_sin; p.seq_len = a->seq_len > 0 ? a->seq_len : 1; p.rope_cols = a->rope_cols;
+  p.dropout_p = a->dropout_p; p.rng = a->rng_state; p.rng_stream = a->rng_stream; p.half_n = a->half_n;
 
-  const long tiles = long((a->M + 2 * BM - 1) / (2 * BM)) * ((a->N + BNP - 1) / BNP) * p.split_k;
+  const long tiles = long((a->M + 2 * BM - 1) / (2 * BM)) * ((a->N + bnp - 1) / bnp) * p.split_k;
   int sms = sm_count();
   if (a->max_ctas > 0 && a->max_ctas < sms) sms = a->max_ctas;
   long pairs = sms / 2;
   if (pairs < 1) pairs = 1;
   if (tiles < pairs) pairs = tiles;
   const int grid = int(pairs * 2);
-  switch (a->epilogue) {
-    case EPI_BF16: return dispatch<EPI_BF16>(a_mn, b_mn, ta, tb, tc, p, grid, stream);
-    case EPI_F32: return dispatch<EPI_F32>(a_mn, b_mn, ta, tb, tc, p, grid, stream);
-    default: return dispatch<EPI_F32_ATOMIC>(a_mn, b_mn, ta, tb, tc, p, grid, stream);
-  }
+  if (epi == EPI_SWIGLU) return dispatch<256, EPI_SWIGLU>(a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
+  if (bnp == 256) return dispatch_epi<256>(epi, a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
+  return dispatch_epi<128>(epi, a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
 }

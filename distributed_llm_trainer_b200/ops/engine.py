@@ -126,9 +126,9 @@ class FusedGPTEngine:
         self.rng_state = torch.tensor([seed & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=self.device)
         self._ws: Dict[Tuple[int, int, bool], _Workspace] = {}
         self.use_graphs = True
-        # epilogue-fusion switches (A/B-able; see profiles/): the SwiGLU' epilogue is currently slower than
-        # GEMM + streaming kernel because its per-thread-row global loads are not coalesced
-        self.fuse_swiglu_bwd = False
+        # epilogue-fusion switch (A/B-able): SwiGLU' inside the down-proj dgrad GEMM (CTA-pair kernel: gate|up
+        # prefetched by TMA into the staging ring) vs GEMM + streaming kernel
+        self.fuse_swiglu_bwd = True
         self.max_ctas = 0            # cap for GEMM grids when a comm kernel needs resident SMs
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         # hooks used by the DDP / FSDP engines

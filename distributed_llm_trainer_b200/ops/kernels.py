@@ -123,7 +123,8 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
         aux=_ptr(aux), ld_aux=0 if aux is None else aux.stride(0), half_n=half_n,
     )
     if pair is None:
-        pair = use_pair_kernel and epilogue <= EPI_F32_ATOMIC and N >= 256 and M >= 256
+        pair = (use_pair_kernel and M >= 256 and N >= 128 and not (a_mn and epilogue > EPI_F32_ATOMIC)
+                and not (epilogue == EPI_SWIGLU and (half_n % 128 or b_mn)))
     _call("b200_gemm2_bf16" if pair else "b200_gemm_bf16", C.byref(args), _stream())
 
 

@@ -218,7 +218,7 @@ class ShardedGPT:
         e.rng_state = torch.tensor([seed & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=self.device)
         e._ws = {}
         e.use_graphs = False
-        e.fuse_swiglu_bwd = False
+        e.fuse_swiglu_bwd = True
         e.max_ctas = 0
         e.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self._LayerWeights = LayerWeights

@@ -8,6 +8,18 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=["1cta", "pair"])
+def _kernel_choice(request):
+    """Every test runs against the single-CTA kernel and against the CTA-pair kernel (which takes over
+    automatically for M >= 256 when enabled)."""
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    prev = k.use_pair_kernel
+    k.use_pair_kernel = request.param == "pair"
+    yield
+    k.use_pair_kernel = prev
+
+
 def _mk(shape, scale=1.0):
     return (torch.randn(*shape, device="cuda") * scale).to(torch.bfloat16)
 
