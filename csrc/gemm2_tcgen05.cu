@@ -32,6 +32,9 @@ constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int kAStage = BM * BK * 2;   // 16 KB
 constexpr int kEpiBuf = 128 * 128;     // staging slot: 128 rows x 128 B
+constexpr int kEpiWarps = 8;           // two per scheduler
+constexpr int kEpiThreads = kEpiWarps * 32;
+constexpr int kThreads = 64 + kEpiThreads;
 
 enum {
   EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ATOMIC = 2, EPI_ROPE_BF16 = 3, EPI_RESID_DROPOUT = 4, EPI_SWIGLU = 5,
@@ -69,12 +72,12 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
-__device__ __forceinline__ float sigmoid_f(float x) { return 1.0f / (1.0f + __expf(-x)); }
+__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.0f, 1.0f + exp2f(-1.4426950408889634f * x)); }
 
 // tma_c: primary output.  tma_x: second tensor -- RESID_DROPOUT: residual (fp32, input); SWIGLU: act (bf16,
 // output); SWIGLU_BWD: saved [gate|up] (bf16, input).
 template <int BNP, bool A_MN, bool B_MN, int EPI>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(192, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
              const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p) {
   using C = Cfg<BNP, EPI>;
@@ -115,7 +118,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(&tmem_full[i], 1);
-      mbar_init(&tmem_empty[i], 8);
+      mbar_init(&tmem_empty[i], 2 * kEpiWarps);
     }
     for (int i = 0; i < 6; ++i) mbar_init(&ld_bar[i], 1);
     fence_barrier_init();
@@ -200,16 +203,19 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     }
   } else {
     // ------------------------------------------------------------------ epilogue warps (both CTAs)
+    // Eight warps: warps e and e+4 share a TMEM lane quarter (row r_in) and split every unit's columns in
+    // halves, so each scheduler has two epilogue warps to overlap tcgen05.ld / smem / MUFU latencies.
     const int q = warp & 3;
+    const int hf = (warp - 2) >> 2;                       // column half owned inside a unit
     const int r_in = q * 32 + lane;                       // row within this CTA's 128 x BNP accumulator
     const int sw = r_in & 7;
     const bool epi_leader = threadIdx.x == 64;
     const uint32_t lane_off = uint32_t(q * 32) << 16;
     const uint32_t epi_base = smem_u32(smem_epi);
-    const int my_tiles = (num_tiles - pair + npairs - 1) / npairs;   // tiles this pair processes (>= 0)
+    const int my_tiles = (num_tiles - pair + npairs - 1) / npairs;   // tiles this pair processes
 
-    // "unit" = the amount of output handled per staging step; units are numbered across tiles so that the
-    // staging ring and the input prefetch run ahead over tile boundaries.
+    // "unit" = the amount of output handled per staging step (128 bytes per row); units are numbered across
+    // tiles so that the staging ring and the input prefetch run ahead over tile boundaries.
     constexpr int kUnitCols = (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC || EPI == EPI_RESID_DROPOUT) ? 32 : 64;
     constexpr int kUnits = (EPI == EPI_SWIGLU) ? BNP / 128 : BNP / kUnitCols;   // per tile
     const long total_units = (long)my_tiles * kUnits;
@@ -221,16 +227,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
       n0 = (r / tiles_m) * BNP;
     };
-    // store-only staging step: slot g % NB
-    uint32_t g = 0;
+    uint32_t g = 0;   // store-only staging ring position
     auto stage_begin = [&]() -> uint32_t {
       if (epi_leader) tma_store_wait_read<NB - 1>();   // the store that last read this slot is done with it
-      named_bar_sync(1, 128);
+      named_bar_sync(1, kEpiThreads);
       return epi_base + (g % NB) * kEpiBuf;
     };
     auto stage_end = [&](const CUtensorMap* map, int col, int row, bool reduce) {
       fence_proxy_async_smem();
-      named_bar_sync(1, 128);
+      named_bar_sync(1, kEpiThreads);
       if (epi_leader) {
         if (reduce) tma_reduce_add_2d(map, smem_epi + (g % NB) * kEpiBuf, col, row);
         else tma_store_2d(map, smem_epi + (g % NB) * kEpiBuf, col, row);
@@ -238,16 +243,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       }
       ++g;
     };
-    auto put_bf16x64 = [&](uint32_t slot, const uint32_t* v0, const uint32_t* v1) {   // fp32 bits -> bf16 row
+    // this thread's 32 bf16 columns (fp32 bits in v) -> chunks hf*4 .. hf*4+3 of its staging row
+    auto put_bf16x32 = [&](uint32_t slot, const uint32_t* v) {
       const uint32_t row_addr = slot + r_in * 128;
 #pragma unroll
-      for (int cc = 0; cc < 8; ++cc) {
-        const uint32_t* v = cc < 4 ? v0 + cc * 8 : v1 + (cc - 4) * 8;
-        st_shared_v4_u32(row_addr + ((cc ^ sw) << 4), pack_bf16x2(__uint_as_float(v[0]), __uint_as_float(v[1])),
-                         pack_bf16x2(__uint_as_float(v[2]), __uint_as_float(v[3])),
-                         pack_bf16x2(__uint_as_float(v[4]), __uint_as_float(v[5])),
-                         pack_bf16x2(__uint_as_float(v[6]), __uint_as_float(v[7])));
-      }
+      for (int cc = 0; cc < 4; ++cc)
+        st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4),
+                         pack_bf16x2(__uint_as_float(v[cc * 8 + 0]), __uint_as_float(v[cc * 8 + 1])),
+                         pack_bf16x2(__uint_as_float(v[cc * 8 + 2]), __uint_as_float(v[cc * 8 + 3])),
+                         pack_bf16x2(__uint_as_float(v[cc * 8 + 4]), __uint_as_float(v[cc * 8 + 5])),
+                         pack_bf16x2(__uint_as_float(v[cc * 8 + 6]), __uint_as_float(v[cc * 8 + 7])));
     };
     auto release_tmem = [&](int buf) {
       tc_fence_before();
@@ -256,29 +261,23 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     };
 
     if constexpr (EPI == EPI_RESID_DROPOUT) {
-      // prefetch the residual two units ahead into the slot that unit will also be stored from
-      auto issue_load = [&](long u) {
-        if (u < total_units) {
+      if (epi_leader) {   // residual prefetch runs two units ahead
+        for (long u = 0; u < 2 && u < total_units; ++u) {
           int m0, n0, c;
           unit_coords(u, m0, n0, c);
           mbar_expect_tx(&ld_bar[u % NB], kEpiBuf);
           tma_load_2d(smem_epi + (u % NB) * kEpiBuf, &tma_x, &ld_bar[u % NB], n0 + c * 32, m0);
         }
-      };
-      if (epi_leader) { issue_load(0); issue_load(1); }
+      }
     }
     if constexpr (EPI == EPI_SWIGLU_BWD) {
-      auto issue_load = [&](long u) {
-        if (u < total_units) {
-          int m0, n0, c;
-          unit_coords(u, m0, n0, c);
-          const int pr = int(u % 3);
-          mbar_expect_tx(&ld_bar[pr], 2 * kEpiBuf);
-          tma_load_2d(smem_epi + (2 * pr) * kEpiBuf, &tma_x, &ld_bar[pr], n0 + c * 64, m0);
-          tma_load_2d(smem_epi + (2 * pr + 1) * kEpiBuf, &tma_x, &ld_bar[pr], p.half_n + n0 + c * 64, m0);
-        }
-      };
-      if (epi_leader) issue_load(0);
+      if (epi_leader && total_units > 0) {   // [gate|up] prefetch runs one unit (a pair of slots) ahead
+        int m0, n0, c;
+        unit_coords(0, m0, n0, c);
+        mbar_expect_tx(&ld_bar[0], 2 * kEpiBuf);
+        tma_load_2d(smem_epi, &tma_x, &ld_bar[0], n0 + c * 64, m0);
+        tma_load_2d(smem_epi + kEpiBuf, &tma_x, &ld_bar[0], p.half_n + n0 + c * 64, m0);
+      }
     }
 
     const bool drop = p.dropout_p > 0.f;
@@ -300,48 +299,65 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       tc_fence_after();
       const uint32_t t_row = tmem_base + lane_off + buf * BNP;
 
-      if constexpr (EPI == EPI_BF16 || EPI == EPI_ROPE_BF16) {
+      if constexpr (EPI == EPI_BF16) {
 #pragma unroll 1
         for (int c = 0; c < kUnits; ++c) {
           const uint32_t slot = stage_begin();
-          uint32_t v0[32], v1[32];
-          tmem_ld_32x32b_x32(t_row + c * 64, v0);
-          tmem_ld_32x32b_x32(t_row + c * 64 + 32, v1);
+          uint32_t v[32];
+          tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, v);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
-          if constexpr (EPI == EPI_ROPE_BF16) {
-            if (n0 + c * 64 < p.rope_cols) {   // one 64-column unit = one head; column j pairs with j + 32
-              const int pos = (row < p.M ? row : 0) % p.seq_len;
-              const float4* cs = reinterpret_cast<const float4*>(p.rope_cos + size_t(pos) * 32);
-              const float4* sn = reinterpret_cast<const float4*>(p.rope_sin + size_t(pos) * 32);
+          put_bf16x32(slot, v);
+          stage_end(&tma_c, n0 + c * 64, m0, false);
+        }
+      } else if constexpr (EPI == EPI_ROPE_BF16) {
+        // one unit = one head; column j (< 32) pairs with j + 32, so both halves are read and each thread
+        // produces its own half.  cos/sin depend on the row only: cached in registers for the whole tile.
+        float cs[32], sn[32];
+        {
+          const int pos = (row < p.M ? row : 0) % p.seq_len;
+          const float4* c4 = reinterpret_cast<const float4*>(p.rope_cos + size_t(pos) * 32);
+          const float4* s4 = reinterpret_cast<const float4*>(p.rope_sin + size_t(pos) * 32);
 #pragma unroll
-              for (int g4 = 0; g4 < 8; ++g4) {
-                const float4 cc = cs[g4], ss = sn[g4];
-                const float cv[4] = {cc.x, cc.y, cc.z, cc.w}, sv[4] = {ss.x, ss.y, ss.z, ss.w};
-#pragma unroll
-                for (int e = 0; e < 4; ++e) {
-                  const float x1 = __uint_as_float(v0[g4 * 4 + e]), x2 = __uint_as_float(v1[g4 * 4 + e]);
-                  v0[g4 * 4 + e] = __float_as_uint(x1 * cv[e] - x2 * sv[e]);
-                  v1[g4 * 4 + e] = __float_as_uint(x2 * cv[e] + x1 * sv[e]);
-                }
-              }
-            }
+          for (int i = 0; i < 8; ++i) {
+            const float4 a = c4[i], b = s4[i];
+            cs[4 * i] = a.x; cs[4 * i + 1] = a.y; cs[4 * i + 2] = a.z; cs[4 * i + 3] = a.w;
+            sn[4 * i] = b.x; sn[4 * i + 1] = b.y; sn[4 * i + 2] = b.z; sn[4 * i + 3] = b.w;
           }
-          put_bf16x64(slot, v0, v1);
+        }
+#pragma unroll 1
+        for (int c = 0; c < kUnits; ++c) {
+          const uint32_t slot = stage_begin();
+          uint32_t v[32];
+          if (n0 + c * 64 < p.rope_cols) {
+            uint32_t w[32];
+            tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, v);          // own half
+            tmem_ld_32x32b_x32(t_row + c * 64 + (hf ^ 1) * 32, w);    // partner half
+            tmem_ld_wait();
+            const float sgn = hf == 0 ? -1.0f : 1.0f;   // first half: x1*c - x2*s ; second half: x2*c + x1*s
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              v[e] = __float_as_uint(__uint_as_float(v[e]) * cs[e] + sgn * __uint_as_float(w[e]) * sn[e]);
+          } else {
+            tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, v);
+            tmem_ld_wait();
+          }
+          if (c == kUnits - 1) release_tmem(buf);
+          put_bf16x32(slot, v);
           stage_end(&tma_c, n0 + c * 64, m0, false);
         }
       } else if constexpr (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC) {
 #pragma unroll 1
         for (int c = 0; c < kUnits; ++c) {
           const uint32_t slot = stage_begin();
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(t_row + c * 32, v);
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
           const uint32_t row_addr = slot + r_in * 128;
 #pragma unroll
-          for (int cc = 0; cc < 8; ++cc)
-            st_shared_v4_u32(row_addr + ((cc ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
+          for (int cc = 0; cc < 4; ++cc)
+            st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
           stage_end(&tma_c, n0 + c * 32, m0, EPI == EPI_F32_ATOMIC);
         }
       } else if constexpr (EPI == EPI_RESID_DROPOUT) {
@@ -359,34 +375,34 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             }
           }
           const uint32_t slot = epi_base + uint32_t(u_glob % NB) * kEpiBuf;
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(t_row + c * 32, v);
+          uint32_t v[16];
+          tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
           mbar_wait(&ld_bar[u_glob % NB], uint32_t(u_glob / NB) & 1);
           const uint32_t row_addr = slot + r_in * 128;
           const int col0 = n0 + c * 32;
 #pragma unroll
-          for (int g8 = 0; g8 < 4; ++g8) {
+          for (int g8 = 0; g8 < 2; ++g8) {
             uint32_t keep = 0xFF;
-            if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + g8), thresh);
+            if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + hf * 2 + g8), thresh);
 #pragma unroll
             for (int hlf = 0; hlf < 2; ++hlf) {
-              const int cc = g8 * 2 + hlf;
-              const uint32_t addr = row_addr + ((cc ^ sw) << 4);
+              const int cl = g8 * 2 + hlf;                 // local 16-byte chunk (4 floats) of this thread's 16 columns
+              const uint32_t addr = row_addr + (((hf * 4 + cl) ^ sw) << 4);
               const uint4 rq = ld_shared_v4(addr);
               const float rr[4] = {__uint_as_float(rq.x), __uint_as_float(rq.y), __uint_as_float(rq.z), __uint_as_float(rq.w)};
               uint32_t o[4];
 #pragma unroll
               for (int e = 0; e < 4; ++e) {
-                const float a = ((keep >> (hlf * 4 + e)) & 1) ? __uint_as_float(v[cc * 4 + e]) * inv_keep : 0.f;
+                const float a = ((keep >> (hlf * 4 + e)) & 1) ? __uint_as_float(v[cl * 4 + e]) * inv_keep : 0.f;
                 o[e] = __float_as_uint(rr[e] + a);
               }
               st_shared_v4_u32(addr, o[0], o[1], o[2], o[3]);
             }
           }
           fence_proxy_async_smem();
-          named_bar_sync(1, 128);
+          named_bar_sync(1, kEpiThreads);
           if (epi_leader) {
             tma_store_2d(&tma_c, smem_epi + (u_glob % NB) * kEpiBuf, col0, m0);
             tma_store_commit();
@@ -396,32 +412,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         // accumulator columns [0, BNP/2) = gate, [BNP/2, BNP) = up, for intermediate columns n0/2 ...
 #pragma unroll 1
         for (int c = 0; c < kUnits; ++c) {
-          uint32_t g0[32], g1[32], u0[32], u1[32];
-          tmem_ld_32x32b_x32(t_row + c * 64, g0);
-          tmem_ld_32x32b_x32(t_row + c * 64 + 32, g1);
-          tmem_ld_32x32b_x32(t_row + BNP / 2 + c * 64, u0);
-          tmem_ld_32x32b_x32(t_row + BNP / 2 + c * 64 + 32, u1);
+          uint32_t gv[32], uv[32];
+          tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, gv);
+          tmem_ld_32x32b_x32(t_row + BNP / 2 + c * 64 + hf * 32, uv);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
-          const int icol = n0 / 2 + c * 64;   // intermediate column
+          const int icol = n0 / 2 + c * 64;   // intermediate column of this unit
           uint32_t slot = stage_begin();
-          put_bf16x64(slot, g0, g1);
+          put_bf16x32(slot, gv);
           stage_end(&tma_c, icol, m0, false);
           slot = stage_begin();
-          put_bf16x64(slot, u0, u1);
+          put_bf16x32(slot, uv);
           stage_end(&tma_c, p.half_n + icol, m0, false);
           // activation from the bf16-rounded gate / up so that backward recomputation is bit-identical
 #pragma unroll
           for (int e = 0; e < 32; ++e) {
-            const float ga = __bfloat162float(__float2bfloat16_rn(__uint_as_float(g0[e])));
-            const float ua = __bfloat162float(__float2bfloat16_rn(__uint_as_float(u0[e])));
-            const float gb = __bfloat162float(__float2bfloat16_rn(__uint_as_float(g1[e])));
-            const float ub = __bfloat162float(__float2bfloat16_rn(__uint_as_float(u1[e])));
-            g0[e] = __float_as_uint(ga * sigmoid_f(ga) * ua);
-            g1[e] = __float_as_uint(gb * sigmoid_f(gb) * ub);
+            const float ga = __bfloat162float(__float2bfloat16_rn(__uint_as_float(gv[e])));
+            const float ua = __bfloat162float(__float2bfloat16_rn(__uint_as_float(uv[e])));
+            gv[e] = __float_as_uint(ga * sigmoid_f(ga) * ua);
           }
           slot = stage_begin();
-          put_bf16x64(slot, g0, g1);
+          put_bf16x32(slot, gv);
           stage_end(&tma_x, icol, m0, false);
         }
       } else {  // EPI_SWIGLU_BWD: acc = d_act; inputs gate/up via TMA; outputs [dgate | dup]
@@ -441,34 +452,32 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
               tma_load_2d(smem_epi + (2 * npr + 1) * kEpiBuf, &tma_x, &ld_bar[npr], p.half_n + pn0 + pc * 64, pm0);
             }
           }
-          uint32_t d0[32], d1[32];
-          tmem_ld_32x32b_x32(t_row + c * 64, d0);
-          tmem_ld_32x32b_x32(t_row + c * 64 + 32, d1);
+          uint32_t d[32];
+          tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, d);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
           mbar_wait(&ld_bar[pr], uint32_t(u_glob / 3) & 1);
           const uint32_t g_row = epi_base + (2 * pr) * kEpiBuf + r_in * 128;
           const uint32_t u_row = g_row + kEpiBuf;
 #pragma unroll
-          for (int cc = 0; cc < 8; ++cc) {
-            const uint32_t ga = g_row + ((cc ^ sw) << 4), ua = u_row + ((cc ^ sw) << 4);
-            const uint4 gq = ld_shared_v4(ga), uq = ld_shared_v4(ua);
+          for (int cc = 0; cc < 4; ++cc) {
+            const uint32_t off = (((hf * 4 + cc) ^ sw) << 4);
+            const uint4 gq = ld_shared_v4(g_row + off), uq = ld_shared_v4(u_row + off);
             const uint32_t gw[4] = {gq.x, gq.y, gq.z, gq.w}, uw[4] = {uq.x, uq.y, uq.z, uq.w};
-            const uint32_t* d = cc < 4 ? d0 + cc * 8 : d1 + (cc - 4) * 8;
             uint32_t og[4], ou[4];
 #pragma unroll
             for (int e = 0; e < 4; ++e) {
               const float2 gg = unpack_bf16x2(gw[e]), uu = unpack_bf16x2(uw[e]);
-              const float da = __uint_as_float(d[2 * e]), db = __uint_as_float(d[2 * e + 1]);
+              const float da = __uint_as_float(d[cc * 8 + 2 * e]), db = __uint_as_float(d[cc * 8 + 2 * e + 1]);
               const float s0 = sigmoid_f(gg.x), s1 = sigmoid_f(gg.y);
               og[e] = pack_bf16x2(da * uu.x * s0 * (1.0f + gg.x * (1.0f - s0)), db * uu.y * s1 * (1.0f + gg.y * (1.0f - s1)));
               ou[e] = pack_bf16x2(da * gg.x * s0, db * gg.y * s1);
             }
-            st_shared_v4_u32(ga, og[0], og[1], og[2], og[3]);
-            st_shared_v4_u32(ua, ou[0], ou[1], ou[2], ou[3]);
+            st_shared_v4_u32(g_row + off, og[0], og[1], og[2], og[3]);
+            st_shared_v4_u32(u_row + off, ou[0], ou[1], ou[2], ou[3]);
           }
           fence_proxy_async_smem();
-          named_bar_sync(1, 128);
+          named_bar_sync(1, kEpiThreads);
           if (epi_leader) {
             tma_store_2d(&tma_c, smem_epi + (2 * pr) * kEpiBuf, n0 + c * 64, m0);
             tma_store_2d(&tma_c, smem_epi + (2 * pr + 1) * kEpiBuf, p.half_n + n0 + c * 64, m0);
@@ -497,7 +506,7 @@ static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMa
     B200_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BNP, EPI>::kSmemTotal));
     configured = true;
   }
-  kfn<<<grid, 192, Cfg<BNP, EPI>::kSmemTotal, stream>>>(ta, tb, tc, tx, p);
+  kfn<<<grid, kThreads, Cfg<BNP, EPI>::kSmemTotal, stream>>>(ta, tb, tc, tx, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -557,13 +566,8 @@ extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) {
   if (epi == EPI_SWIGLU_BWD) B200_REQUIRE(a->N == a->half_n && a->aux != nullptr, "gemm2: SwiGLU' needs N == half_n and the saved [gate|up]");
 
   // tile width: 256 unless the narrower pair tile fills the machine better (N = 768/1024 with few row tiles)
-  int bnp = a->tile_n == 128 ? 128 : 256;
-  if (a->tile_n != 128 && a->tile_n != 256 && epi != EPI_SWIGLU) {
-    const int pairs_hw = sm_count() / 2;
-    const int split = a->split_k > 0 ? a->split_k : 1;
-    auto waves = [&](int w) { long t = long((a->M + 255) / 256) * ((a->N + w - 1) / w) * split; return double((t + pairs_hw - 1) / pairs_hw); };
-    bnp = (waves(128) * 0.56 < waves(256)) ? 128 : 256;
-  }
+  // 256-wide pair tile unless the caller forces 128 (measured slower on every model shape, kept for narrow N)
+  int bnp = (a->tile_n == 128 || a->N < 256) ? 128 : 256;
   if (epi == EPI_SWIGLU) bnp = 256;
 
   CUtensorMap ta, tb, tc, tx;
