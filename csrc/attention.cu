@@ -9,8 +9,8 @@
 // Forward CTA = (q block of 128 rows, head, batch), 6 warps:
 //   warp 0     TMA producer: Q once, K/V tiles through 2-stage rings
 //   warp 1     MMA issuer:   S_j = Q K_j^T  (TMEM, double buffered)  and  O_j = P_j V_j (TMEM, double buffered)
-//   warps 2-9  softmax: two threads per query row, each owning 64 of the 128 score columns (two warps
-//              per scheduler hide the tcgen05.ld / MUFU latencies one warp cannot).  tcgen05.ld S ->
+//   warps 2-17 softmax: four threads per query row, each owning 32 of the 128 score columns (four warps
+//              per scheduler: measured, one or two cannot hide the fixed-latency dependency stalls).  tcgen05.ld S ->
 //              online softmax in the exp2 domain (row max exchanged once per tile through smem) ->
 //              dropout -> bf16 P tile written to 128B-swizzled smem (A operand of P V) -> running O kept
 //              in registers: o = o * alpha + O_j (no TMEM rescale pass).
@@ -68,14 +68,14 @@ struct FwdSmem {
   static constexpr int kV = kK + 2 * kTile;        // 2 stages
   static constexpr int kP = kV + 2 * kTile;        // 2 buffers x 32 KB
   static constexpr int kBars = kP + 2 * kPTile;
-  static constexpr int kXchg = kBars + 256;                 // float [2][2][128] row-max exchange
-  static constexpr int kTotal = kXchg + 2 * 2 * 128 * 4 + 1024;
+  static constexpr int kXchg = kBars + 256;                 // float [2][4][128] row-max exchange
+  static constexpr int kTotal = kXchg + 2 * 4 * 128 * 4 + 1024;
 };
 
-constexpr int kSoftmaxWarps = 8;
+constexpr int kSoftmaxWarps = 16;   // four per scheduler: each thread owns one row x 32 score columns
 constexpr int kAttnThreads = 64 + kSoftmaxWarps * 32;
 
-__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 256;" ::: "memory"); }
+__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
@@ -185,7 +185,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     }
   } else {
     const int qd = warp & 3;
-    const int hf = (warp - 2) >> 2;               // which 64-column half of the score tile this thread owns
+    const int qt = (warp - 2) >> 2;               // which 32-column quarter of the score tile this thread owns
     const int r = qd * 32 + lane;                 // row within the q tile
     const int qrow = qi * kBlk + r;               // position in the sequence
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
@@ -194,22 +194,22 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
     const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
-    float* xchg = reinterpret_cast<float*>(smem + FwdSmem::kXchg);
+    float* xchg = reinterpret_cast<float*>(smem + FwdSmem::kXchg);   // [2][4][128]
 
     float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-    float o[32];
+    float o[16];
 #pragma unroll
-    for (int e = 0; e < 32; ++e) o[e] = 0.f;
+    for (int e = 0; e < 16; ++e) o[e] = 0.f;
 
     auto fold_o = [&](int pb, uint32_t parity, float alpha) {
       mbar_wait(&o_full[pb], parity);
       tc_fence_after();
-      uint32_t v[32];
+      uint32_t v[16];
       __syncwarp();
-      tmem_ld_32x32b_x32(tO[pb] + lane_off + hf * 32, v);
+      tmem_ld_32x32b_x16(tO[pb] + lane_off + qt * 16, v);
       tmem_ld_wait();
 #pragma unroll
-      for (int e = 0; e < 32; ++e) o[e] = o[e] * alpha + __uint_as_float(v[e]);
+      for (int e = 0; e < 16; ++e) o[e] = o[e] * alpha + __uint_as_float(v[e]);
     };
 
     for (int j = 0; j < nkv; ++j) {
@@ -218,51 +218,46 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       const bool diag = (j == qi);
       mbar_wait(&s_full[st], ph);
       tc_fence_after();
-      // pass 1: maximum over this thread's 64 columns, then exchange with the partner thread
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        __syncwarp();
-        tmem_ld_32x32b_x32(tS[st] + lane_off + hf * 64 + c * 32, v);
-        tmem_ld_wait();
+      // this thread's 32 scores stay in registers for both the max and the exp pass
+      uint32_t v[32];
+      __syncwarp();
+      tmem_ld_32x32b_x32(tS[st] + lane_off + qt * 32, v);
+      tmem_ld_wait();
+      float s[32];
 #pragma unroll
-        for (int e = 0; e < 32; ++e) {
-          const float sc = __uint_as_float(v[e]) * kScale2;
-          if (!diag || (hf * 64 + c * 32 + e) <= r) mx = fmaxf(mx, sc);
-        }
+      for (int e = 0; e < 32; ++e) {
+        s[e] = __uint_as_float(v[e]) * kScale2;
+        if (diag && (qt * 32 + e) > r) s[e] = -INFINITY;
       }
-      xchg[(st * 2 + hf) * 128 + r] = mx;
+      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains instead of one serial max
+#pragma unroll
+      for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], s[e]);
+      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+      xchg[(st * 4 + qt) * 128 + r] = mx;
       softmax_bar_sync();
-      mx = fmaxf(fmaxf(mx, xchg[(st * 2 + (hf ^ 1)) * 128 + r]), m);
+#pragma unroll
+      for (int t = 0; t < 4; ++t) mx = fmaxf(mx, xchg[(st * 4 + t) * 128 + r]);
+      mx = fmaxf(mx, m);
       const float m_use = (mx == -INFINITY) ? 0.f : mx;
       const float alpha = exp2f(m - m_use);
-      l *= alpha;
-      // pass 2: probabilities -> smem (bf16, dropout applied, unnormalised)
-      const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + hf * kTile;
-#pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
-        uint32_t v[32];
-        __syncwarp();
-        tmem_ld_32x32b_x32(tS[st] + lane_off + hf * 64 + c * 32, v);
-        tmem_ld_wait();
+      // probabilities -> smem (bf16, dropout applied, unnormalised)
+      const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + (qt >> 1) * kTile;
+      float l4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint32_t keep = 0xFF;
-          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + hf * 64 + c * 32 + g * 8) >> 3), thresh);
-          float pv[8];
+      for (int g = 0; g < 4; ++g) {
+        uint32_t keep = 0xFF;
+        if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3), thresh);
+        float pv[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int col = hf * 64 + c * 32 + g * 8 + e;
-            float pe = exp2f(__uint_as_float(v[g * 8 + e]) * kScale2 - m_use);
-            if (diag && col > r) pe = 0.f;
-            l += pe;
-            pv[e] = ((keep >> e) & 1) ? pe : 0.f;
-          }
-          st_shared_v4(swz(sub, r, c * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
-                       pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
+        for (int e = 0; e < 8; ++e) {
+          const float pe = exp2f(s[g * 8 + e] - m_use);   // masked entries are exp2(-inf) = 0
+          l4[e & 3] += pe;
+          pv[e] = ((keep >> e) & 1) ? pe : 0.f;
         }
+        st_shared_v4(swz(sub, r, (qt & 1) * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
+                     pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
       }
+      l = l * alpha + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
@@ -282,20 +277,20 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       m = m_use;
     }
     fold_o((nkv - 1) & 1, ((nkv - 1) >> 1) & 1, alpha_prev);
-    // total row sum = the two column-halves' partial sums (same running max on both threads)
+    // total row sum = the four column-quarters' partial sums (same running max on all four threads)
     softmax_bar_sync();
-    xchg[hf * 128 + r] = l;
+    xchg[qt * 128 + r] = l;
     softmax_bar_sync();
-    l += xchg[(hf ^ 1) * 128 + r];
+    l = (xchg[r] + xchg[128 + r]) + (xchg[256 + r] + xchg[384 + r]);
     if (qrow < p.S) {
       const float inv = (drop ? 1.f / (1.f - p.p_drop) : 1.f) / l;
-      __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD + hf * 32;
+      __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD + qt * 16;
 #pragma unroll
-      for (int g = 0; g < 4; ++g)
+      for (int g = 0; g < 2; ++g)
         *reinterpret_cast<uint4*>(dst + g * 8) =
             make_uint4(pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv), pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv),
                        pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv), pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv));
-      if (hf == 0) p.lse[size_t(b * p.H + hd) * p.S + qrow] = m + log2f(l);
+      if (qt == 0) p.lse[size_t(b * p.H + hd) * p.S + qrow] = m + log2f(l);
     }
   }
 
@@ -465,7 +460,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
   } else {
     const int qd = warp & 3;
-    const int hf = (warp - 2) >> 2;   // two threads per row: each owns 64 kv columns / 32 head-dim columns
+    const int qt = (warp - 2) >> 2;   // four threads per row: each owns 32 kv columns / 16 head-dim columns
     const int r = qd * 32 + lane;
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
@@ -473,26 +468,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const float inv_keep = drop ? 1.f / (1.f - p.p_drop) : 1.f;
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
-    const uint32_t p_base = smem_u32(smem + BwdSmem::kP), ds_base = smem_u32(smem + BwdSmem::kdS);
+    const uint32_t p_sub = smem_u32(smem + BwdSmem::kP) + (qt >> 1) * kTile;
+    const uint32_t ds_sub = smem_u32(smem + BwdSmem::kdS) + (qt >> 1) * kTile;
 
     auto drain_dq = [&](int it) {
       const int qrow = (j + it) * kBlk + r;
       mbar_wait(dq_full, it & 1);
       tc_fence_after();
-      float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + hf * 32;
-      {
-        uint32_t v[32];
-        __syncwarp();
-        tmem_ld_32x32b_x32(tdQ + lane_off + hf * 32, v);
-        tmem_ld_wait();
-        if (qrow < p.S) {
+      float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + qt * 16;
+      uint32_t v[16];
+      __syncwarp();
+      tmem_ld_32x32b_x16(tdQ + lane_off + qt * 16, v);
+      tmem_ld_wait();
+      if (qrow < p.S) {
 #pragma unroll
-          for (int g = 0; g < 8; ++g)
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 4),
-                         "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
-                         "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
-                         : "memory");
-        }
+        for (int g = 0; g < 4; ++g)
+          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 4),
+                       "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
+                       "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
+                       : "memory");
       }
       tc_fence_before();
       __syncwarp();
@@ -511,35 +505,31 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
-#pragma unroll 1
-      for (int c = 0; c < 2; ++c) {
-        uint32_t sv[32], dv[32];
-        __syncwarp();
-        tmem_ld_32x32b_x32(tS + lane_off + hf * 64 + c * 32, sv);
-        tmem_ld_32x32b_x32(tdP + lane_off + hf * 64 + c * 32, dv);
-        tmem_ld_wait();
-        const int sub = hf * kTile;
+      uint32_t sv[32], dv[32];
+      __syncwarp();
+      tmem_ld_32x32b_x32(tS + lane_off + qt * 32, sv);
+      tmem_ld_32x32b_x32(tdP + lane_off + qt * 32, dv);
+      tmem_ld_wait();
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
-          uint32_t keep = 0xFF;
-          if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + hf * 64 + c * 32 + g * 8) >> 3), thresh);
-          float pd[8], ds[8];
+      for (int g = 0; g < 4; ++g) {
+        uint32_t keep = 0xFF;
+        if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3), thresh);
+        float pd[8], ds[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            const int col = hf * 64 + c * 32 + g * 8 + e;
-            float pe = exp2f(__uint_as_float(sv[g * 8 + e]) * kScale2 - lse2);
-            if (diag && col > r) pe = 0.f;
-            const bool k1 = (keep >> e) & 1;
-            const float dpe = k1 ? __uint_as_float(dv[g * 8 + e]) * inv_keep : 0.f;
-            ds[e] = pe * (dpe - dl) * kScale;
-            pd[e] = k1 ? pe * inv_keep : 0.f;
-          }
-          const int cc = c * 4 + g;
-          st_shared_v4(swz(p_base + sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
-                       pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
-          st_shared_v4(swz(ds_base + sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
-                       pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+        for (int e = 0; e < 8; ++e) {
+          const int col = qt * 32 + g * 8 + e;
+          float pe = exp2f(__uint_as_float(sv[g * 8 + e]) * kScale2 - lse2);
+          if (diag && col > r) pe = 0.f;
+          const bool k1 = (keep >> e) & 1;
+          const float dpe = k1 ? __uint_as_float(dv[g * 8 + e]) * inv_keep : 0.f;
+          ds[e] = pe * (dpe - dl) * kScale;
+          pd[e] = k1 ? pe * inv_keep : 0.f;
         }
+        const int cc = (qt & 1) * 4 + g;
+        st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
+                     pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
+        st_shared_v4(swz(ds_sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                     pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
       }
       tc_fence_before();
       fence_proxy_async_smem();
@@ -551,21 +541,21 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
     drain_dq(niter - 1);
 
-    // dK / dV of this kv block: thread r owns kv row r
+    // dK / dV of this kv block: thread (r, qt) owns kv row r, head-dim columns [16 qt, 16 qt + 16)
     mbar_wait(acc_full, 0);
     tc_fence_after();
     const int kvrow = j * kBlk + r;
-    __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD + hf * 32;
+    __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD + qt * 16;
     __nv_bfloat16* dv_dst = dk_dst + h;
     {
-      uint32_t kv_[32], vv_[32];
+      uint32_t kv_[16], vv_[16];
       __syncwarp();
-      tmem_ld_32x32b_x32(tdK + lane_off + hf * 32, kv_);
-      tmem_ld_32x32b_x32(tdV + lane_off + hf * 32, vv_);
+      tmem_ld_32x32b_x16(tdK + lane_off + qt * 16, kv_);
+      tmem_ld_32x32b_x16(tdV + lane_off + qt * 16, vv_);
       tmem_ld_wait();
       if (kvrow < p.S) {
 #pragma unroll
-        for (int g = 0; g < 4; ++g) {
+        for (int g = 0; g < 2; ++g) {
           *reinterpret_cast<uint4*>(dk_dst + g * 8) = make_uint4(
               pack_bf16x2(__uint_as_float(kv_[g * 8 + 0]), __uint_as_float(kv_[g * 8 + 1])),
               pack_bf16x2(__uint_as_float(kv_[g * 8 + 2]), __uint_as_float(kv_[g * 8 + 3])),
