@@ -36,7 +36,9 @@ from ..parallel.flat import FlatParamStore
 from . import kernels as K
 from .reference import rope_tables
 
-_LM_CHUNK_BYTES = 96 << 20  # logits chunk sized to stay L2-resident (126 MB L2)
+# bf16 logits chunk.  Measured (benchmarks/bench_lmchunk.py, small model, 8192 rows): 24 MB 18.3 ms/micro-step,
+# 96 MB 13.2, 192 MB 12.6, 288-420 MB 12.5, one 824 MB chunk 12.7 -- GEMM efficiency at large M beats L2 residency.
+_LM_CHUNK_BYTES = 416 << 20
 
 
 @dataclass
