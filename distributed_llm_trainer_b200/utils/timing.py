@@ -8,7 +8,6 @@ from __future__ import annotations
 import statistics
 import subprocess
 import threading
-import time
 from typing import Dict, List, Optional
 
 import torch
@@ -30,31 +29,89 @@ class CudaStepTimer:
         self.ms = self.start.elapsed_time(self.stop)
 
 
+# NVML clocks-event-reason bits (nvml.h)
+_REASONS = {
+    0x0000000000000004: "sw_power_cap",
+    0x0000000000000008: "hw_slowdown",
+    0x0000000000000020: "sw_thermal_slowdown",
+    0x0000000000000040: "hw_thermal_slowdown",
+    0x0000000000000080: "hw_power_brake_slowdown",
+}
+
+
 class ClockSampler:
-    """Samples ``nvidia-smi`` SM clocks / throttle reasons in a background thread during a timed region."""
+    """Samples SM clocks and throttle reasons DURING a timed region from a background thread.
+    Uses NVML directly (a sample every ~20 ms); falls back to polling ``nvidia-smi`` when NVML is unusable."""
 
     QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
              "clocks_event_reasons.sw_power_cap")
 
-    def __init__(self, gpu_index: int = 0, period_s: float = 0.2):
+    def __init__(self, gpu_index: int = 0, period_s: float = 0.02):
         self.gpu_index = gpu_index
         self.period_s = period_s
-        self.samples: List[List[str]] = []
+        self.sm: List[float] = []
+        self.sm_max: Optional[float] = None
+        self.power: List[float] = []
+        self.reasons = set()
+        self.source = "none"
         self._stop = threading.Event()
         self._thread: Optional[threading.Thread] = None
 
-    def _run(self):
+    # ---- NVML path ------------------------------------------------------------------------------------
+    def _run_nvml(self) -> bool:
+        try:
+            import pynvml as N
+
+            N.nvmlInit()
+            idx = self.gpu_index
+            vis = [v for v in (__import__("os").environ.get("CUDA_VISIBLE_DEVICES") or "").split(",") if v.strip()]
+            if vis and idx < len(vis) and vis[idx].strip().isdigit():
+                idx = int(vis[idx])
+            h = N.nvmlDeviceGetHandleByIndex(idx)
+            self.sm_max = float(N.nvmlDeviceGetMaxClockInfo(h, N.NVML_CLOCK_SM))
+        except Exception:
+            return False
+        self.source = "nvml"
+        get_reasons = getattr(N, "nvmlDeviceGetCurrentClocksEventReasons", None) or getattr(
+            N, "nvmlDeviceGetCurrentClocksThrottleReasons", None)
+        while not self._stop.is_set():
+            try:
+                self.sm.append(float(N.nvmlDeviceGetClockInfo(h, N.NVML_CLOCK_SM)))
+                self.power.append(N.nvmlDeviceGetPowerUsage(h) / 1000.0)
+                if get_reasons is not None:
+                    bits = int(get_reasons(h))
+                    for bit, name in _REASONS.items():
+                        if bits & bit:
+                            self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(self.period_s)
+        return True
+
+    # ---- nvidia-smi fallback ------------------------------------------------------------------------------
+    def _run_smi(self) -> None:
+        self.source = "nvidia-smi"
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         while not self._stop.is_set():
             try:
                 out = subprocess.run(["nvidia-smi", f"--query-gpu={self.QUERY}", "--format=csv,noheader,nounits",
                                       "-i", str(self.gpu_index)], capture_output=True, text=True, timeout=5).stdout
                 row = [c.strip() for c in out.strip().split(",")]
                 if len(row) >= 7:
-                    self.samples.append(row)
+                    self.sm.append(float(row[0]))
+                    self.sm_max = float(row[1])
+                    self.power.append(float(row[2]))
+                    for name, val in zip(names, row[3:7]):
+                        if val.lower().startswith("active"):
+                            self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(self.period_s)
+            self._stop.wait(max(self.period_s, 0.1))
+
+    def _run(self):
+        if not self._run_nvml():
+            self._run_smi()
 
     def __enter__(self):
         self._thread = threading.Thread(target=self._run, daemon=True)
@@ -67,16 +124,6 @@ class ClockSampler:
             self._thread.join(timeout=10)
 
     def summary(self) -> Dict[str, object]:
-        sm, mx, reasons = [], [], set()
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        for row in self.samples:
-            try:
-                sm.append(float(row[0]))
-                mx.append(float(row[1]))
-            except ValueError:
-                continue
-            for name, val in zip(names, row[3:7]):
-                if val.lower().startswith("active"):
-                    reasons.add(name)
-        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "samples": len(sm), "reasons": sorted(reasons)}
+        return {"sm_mhz": statistics.median(self.sm) if self.sm else None, "sm_max_mhz": self.sm_max,
+                "power_w_max": max(self.power) if self.power else None, "samples": len(self.sm),
+                "reasons": sorted(self.reasons), "source": self.source}
