@@ -28,6 +28,7 @@ def host_batches(n, vocab, seed):
 
 
 def main():
+    global MICRO_BATCH
     p = argparse.ArgumentParser()
     p.add_argument("--gpus", type=int, default=1)
     p.add_argument("--steps", type=int, default=5)
@@ -42,7 +43,6 @@ def main():
     rank, world, local = dist_info()
     import torch
 
-    global MICRO_BATCH
     MICRO_BATCH = args.batch_size
     if args.impl == "reference":
         sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))

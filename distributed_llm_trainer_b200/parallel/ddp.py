@@ -120,7 +120,12 @@ class NVLinkGradSync:
         self.optimizer = None
         self.comm_stream = torch.cuda.Stream(device=dev)
         self.max_ctas = 0
+        # fork per-unit reductions under the last backward (B200_DDP_OVERLAP=0: reduce everything after it)
+        self.overlap = __import__("os").environ.get("B200_DDP_OVERLAP", "1") != "0"
+        self.comm_ctas = 32          # small grid: shares the SMs with the backward GEMMs it overlaps
         self._last = False
+        self._overlapped = False
+        self._units_done = 0
 
     def owned_ranges(self) -> List[Tuple[int, int]]:
         return self.ranges
@@ -129,7 +134,31 @@ class NVLinkGradSync:
         self.optimizer = opt
 
     def begin_micro_step(self, last: bool) -> None:
+        """Before each micro-step.  On the last one (the only one whose gradients are final -- the
+        ``no_sync`` rule of the reference, ddp_trainer.py:329-332) the engine reports every unit as soon as
+        its backward is done, and that unit's slice reduction is forked onto the comm stream so it overlaps
+        the rest of the backward pass (reference: DDP bucket hooks)."""
         self._last = last
+        self._overlapped = False
+        if last and self.overlap:
+            self.sumsq.zero_()
+            self._units_done = 0
+            self.engine.grad_ready_hook = self._on_unit_ready
+            self._overlapped = True
+
+    def _on_unit_ready(self, unit: int) -> None:
+        from ..ops import kernels as K
+
+        cur = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(cur)
+        self.comm_stream.wait_event(ev)
+        lo, hi = self.ranges[unit]
+        with torch.cuda.stream(self.comm_stream):
+            self.pads.barrier()      # every rank has finished this unit's gradients
+            K.reduce_scatter_f32(self.grad_buf.ptrs, self.store.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1],
+                                 self.rank, self.world, self.comm_ctas)
+        self._units_done += 1
 
     # ---- the fused step --------------------------------------------------------------------------------
     def finish_and_step(self, grad_clip: float, norm_out: Optional[torch.Tensor] = None) -> None:
@@ -139,12 +168,17 @@ class NVLinkGradSync:
         g0 = opt.param_groups[0]
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
         opt.step_count += 1
-        self.sumsq.zero_()
-        # every rank's backward has finished writing its gradients
-        self.pads.barrier()
-        for lo, hi in self.ranges:
-            K.reduce_scatter_f32(self.grad_buf.ptrs, st.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1], self.rank,
-                                 self.world, self.max_ctas)
+        if self._overlapped:
+            assert self._units_done == len(self.ranges), "a unit never reported its gradients"
+            self.engine.grad_ready_hook = None
+            torch.cuda.current_stream().wait_stream(self.comm_stream)
+        else:
+            self.sumsq.zero_()
+            # every rank's backward has finished writing its gradients
+            self.pads.barrier()
+            for lo, hi in self.ranges:
+                K.reduce_scatter_f32(self.grad_buf.ptrs, st.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1], self.rank,
+                                     self.world, self.max_ctas)
         # global gradient norm: sum of the per-rank partials (identical summation order everywhere)
         self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
         K.clip_coef(self.sumsq_total, float(grad_clip), 1.0, opt.grad_scale, norm_out)

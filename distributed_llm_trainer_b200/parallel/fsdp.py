@@ -386,6 +386,13 @@ class ShardedGPT:
         opt_state["step"] += 1
         st = self.store
         b1, b2 = betas
+        if self.cpu_offload:
+            self._step_offloaded(opt_state, lr, b1, b2, eps, wd)
+            self.grad_shard.zero_()
+            self.pads.barrier()
+            self._root_done = None
+            self._root_stale = True
+            return
         for u, (a, b) in enumerate(self.ranges):
             if b <= a:
                 continue
@@ -400,6 +407,32 @@ class ShardedGPT:
         self.pads.barrier()
         self._root_done = None
         self._root_stale = True
+
+    # ------------------------------------------------------------------------------------------ CPU offload
+    def _step_offloaded(self, opt_state, lr, b1, b2, eps, wd) -> None:
+        """``--cpu_offload`` (reference: ``CPUOffload(offload_params=True)``, fsdp_trainer.py:300-301): the fp32
+        master shard and both AdamW moments live in pinned host memory; the clipped gradient shard goes
+        device -> host, AdamW runs on the CPU, the new bf16 shard comes back host -> device."""
+        from ..ops.optim import adamw_reference_
+
+        if not hasattr(self, "_host"):
+            pin = dict(dtype=torch.float32, pin_memory=True)
+            master = torch.empty(self.shard_total, **pin)
+            for u, (a, b) in enumerate(self.ranges):
+                master[self.shard_off[u]: self.shard_off[u] + b - a].copy_(self.store.master[a:b])
+            self._host = {"master": master, "grad": torch.empty(self.shard_total, **pin),
+                          "bf16": torch.empty(self.shard_total, dtype=torch.bfloat16, pin_memory=True)}
+        host = self._host
+        scaled = self.grad_shard * opt_state["grad_scale"]          # clip coefficient applied on the device
+        host["grad"].copy_(scaled, non_blocking=True)
+        torch.cuda.current_stream().synchronize()
+        m, v = opt_state["exp_avg"], opt_state["exp_avg_sq"]       # host tensors in this mode
+        ones = torch.ones(1)
+        adamw_reference_(host["master"], host["grad"], m, v, ones, opt_state["step"], lr, b1, b2, eps, wd, 1.0)
+        host["bf16"].copy_(host["master"])
+        self.shard_bf16.local.copy_(host["bf16"], non_blocking=True)
+        for u, (a, b) in enumerate(self.ranges):                    # keep the device copy of the owned slices current
+            self.store.master[a:b].copy_(host["master"][self.shard_off[u]: self.shard_off[u] + b - a], non_blocking=True)
 
     # ------------------------------------------------------------------------------------------ checkpoints
     def gather_full_master(self) -> None:

@@ -87,6 +87,15 @@ class DistributedTrainer:
             else:
                 self.dtype = torch.float32
                 self.autocast_ctx = nullcontext()
+        elif getattr(torch.backends, "mps", None) is not None and torch.backends.mps.is_available():
+            # reference ddp_trainer.py:120-146: Apple-silicon path (fp16 autocast or fp32), kept for parity
+            self.device = torch.device("mps")
+            if mp == "fp16":
+                self.dtype = torch.float16
+                self.autocast_ctx = torch.autocast(device_type="mps", dtype=torch.float16)
+            else:
+                self.dtype = torch.float32
+                self.autocast_ctx = nullcontext()
         else:
             self.device = torch.device("cpu")
             self.dtype = torch.float32

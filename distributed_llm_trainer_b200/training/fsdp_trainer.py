@@ -124,8 +124,11 @@ class FSDPTrainer:
             self.optimizer = FlatAdamW(sh.store, ranges=[(0, 0)], **kw)
             dev = self.device
             self.opt_state = {
-                "exp_avg": torch.zeros(sh.shard_total, dtype=torch.float32, device=dev),
-                "exp_avg_sq": torch.zeros(sh.shard_total, dtype=torch.float32, device=dev),
+                # --cpu_offload keeps the moments (and the fp32 master shard) in pinned host memory
+                "exp_avg": (torch.zeros(sh.shard_total, dtype=torch.float32, pin_memory=True) if sh.cpu_offload
+                            else torch.zeros(sh.shard_total, dtype=torch.float32, device=dev)),
+                "exp_avg_sq": (torch.zeros(sh.shard_total, dtype=torch.float32, pin_memory=True) if sh.cpu_offload
+                               else torch.zeros(sh.shard_total, dtype=torch.float32, device=dev)),
                 "step": 0, "grad_scale": self.optimizer.grad_scale, "decay": self.optimizer._decay,
             }
         elif self.engine is not None:
@@ -209,8 +212,8 @@ class FSDPTrainer:
         if self.sharded is not None:
             sh = self.sharded
             sh.gather_full_master()
-            fm = sh.gather_flat(self.opt_state["exp_avg"]).cpu()
-            fv = sh.gather_flat(self.opt_state["exp_avg_sq"]).cpu()
+            fm = sh.gather_flat(self.opt_state["exp_avg"].to(self.device)).cpu()
+            fv = sh.gather_flat(self.opt_state["exp_avg_sq"].to(self.device)).cpu()
             opt.step_count = self.opt_state["step"]
             return {"model": self.model.state_dict(), "optimizer": opt.state_dict(fm, fv)}
         if self.grad_sync is not None:
@@ -253,6 +256,8 @@ class FSDPTrainer:
             full.load_state_dict(ckpt["optimizer"])
             sh.scatter_flat(full.exp_avg, self.opt_state["exp_avg"])
             sh.scatter_flat(full.exp_avg_sq, self.opt_state["exp_avg_sq"])
+            if hasattr(sh, "_host"):
+                del sh._host                      # host master shard is rebuilt from the loaded weights
             self.opt_state["step"] = full.step_count
             opt.step_count = full.step_count
             del full

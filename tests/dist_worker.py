@@ -136,11 +136,12 @@ def mode_ddp(tmp):
     assert abs(a["loss"] - b["loss"]) < (1e-2 if GPU else 1e-5) * abs(a["loss"]), (a, b)
 
 
-def mode_fsdp(tmp, strategy):
+def mode_fsdp(tmp, strategy, offload=False):
     ga, steps = 2, 3
     tcfg = TrainingConfig.fsdp_defaults(batch_size=2, gradient_accumulation_steps=ga, max_steps=50, warmup_steps=2,
                                         seed=0, backend=BACKEND, checkpoint_dir=tmp)
-    fcfg = FSDPConfig(sharding_strategy=strategy, mixed_precision=MP, activation_checkpointing=True)
+    fcfg = FSDPConfig(sharding_strategy=strategy, mixed_precision=MP, activation_checkpointing=True,
+                      cpu_offload=offload)
     tr = FSDPTrainer(GPTConfig(**CFG), tcfg, fcfg)
     rank, world = tr.rank, tr.world_size
     solo = single_process_reference("fsdp", world, ga, steps, strategy)
@@ -254,7 +255,8 @@ def main():
     if mode == "ddp":
         mode_ddp(tmp)
     elif mode.startswith("fsdp"):
-        mode_fsdp(tmp, mode.split(":")[1])
+        parts = mode.split(":")
+        mode_fsdp(tmp, parts[1], offload=len(parts) > 2 and parts[2] == "offload")
     elif mode == "comm":
         mode_comm(tmp)
     else:

@@ -23,7 +23,8 @@ def _torchrun(mode, tmp, nproc, port):
 
 
 @pytest.mark.parametrize("mode,port", [("comm", 29711), ("ddp", 29712), ("fsdp:FULL_SHARD", 29713),
-                                       ("fsdp:SHARD_GRAD_OP", 29714), ("fsdp:NO_SHARD", 29715)])
+                                       ("fsdp:SHARD_GRAD_OP", 29714), ("fsdp:NO_SHARD", 29715),
+                                       ("fsdp:FULL_SHARD:offload", 29716)])
 def test_multi_gpu(mode, port, tmp_path):
     n = _ngpu()
     if n < 2:
