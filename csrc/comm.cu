@@ -73,7 +73,19 @@ __device__ __forceinline__ void pad_barrier(const PeerTable& pads, int rank, int
   __syncthreads();
 }
 
-__global__ void comm_barrier_kernel(PeerTable pads, int rank, int world, uint32_t epoch) {
+// The epoch of a pad operation is "how many pad operations this rank has executed", kept in device memory and
+// bumped by the kernel itself: nothing host-side is baked into the launch, so the kernels can be captured in
+// a CUDA graph and replayed.  Every rank runs the same stream-ordered sequence of pad operations, so the
+// counters agree.  (Invariant for callers: never have pad operations in flight on two streams at once.)
+__device__ __forceinline__ uint32_t next_epoch(unsigned int* counter) {
+  __shared__ uint32_t s_epoch;
+  if (threadIdx.x == 0) s_epoch = atomicAdd(counter, 1u) + 1u;
+  __syncthreads();
+  return s_epoch;
+}
+
+__global__ void comm_barrier_kernel(PeerTable pads, int rank, int world, unsigned int* counter) {
+  const uint32_t epoch = next_epoch(counter);
   pad_barrier(pads, rank, world, epoch, 0);
 }
 
@@ -182,9 +194,10 @@ adamw_bcast_kernel(float* __restrict__ master, const float* __restrict__ grad, f
 
 // Each rank contributes `n` floats; result (sum over ranks, identical order on every rank) in out[].
 // Exchange area: row 1.. of the signal pads, float slots [rank][n] (n <= 8).
-__global__ void allreduce_scalars_kernel(PeerTable pads, PeerTable xchg, int rank, int world, uint32_t epoch,
+__global__ void allreduce_scalars_kernel(PeerTable pads, PeerTable xchg, int rank, int world, unsigned int* counter,
                                          const float* __restrict__ in, float* __restrict__ out, int n) {
   const int t = threadIdx.x;
+  const uint32_t epoch = next_epoch(counter);
   // xchg.p[r] -> float area [2][kMaxRanks][8] on rank r, double buffered by epoch parity so a fast
   // rank's next exchange cannot overwrite values a slow rank is still summing
   const int par = (epoch & 1) * kMaxRanks * 8;
@@ -273,10 +286,11 @@ extern "C" {
 
 int b200_comm_pad_bytes(void) { return kMaxRanks * 4 * 4 + 2 * kMaxRanks * 8 * 4; }
 
-int b200_comm_barrier(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, void* stream) {
+int b200_comm_barrier(const void* const* pad_ptrs, int rank, int world, unsigned int* epoch_counter, void* stream) {
   PeerTable pads;
   if (int rc = fill_table(&pads, pad_ptrs, world)) return rc;
-  comm_barrier_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, rank, world, epoch);
+  B200_REQUIRE(epoch_counter != nullptr, "comm_barrier: epoch counter (device uint32) required");
+  comm_barrier_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, rank, world, epoch_counter);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -323,14 +337,15 @@ int b200_adamw_bcast(float* master, const float* grad, float* exp_avg, float* ex
   return 0;
 }
 
-int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, const float* in,
-                           float* out, int n, void* stream) {
+int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, unsigned int* epoch_counter,
+                           const float* in, float* out, int n, void* stream) {
   B200_REQUIRE(n >= 1 && n <= 8, "allreduce_scalars: n must be in [1,8]");
+  B200_REQUIRE(epoch_counter != nullptr, "allreduce_scalars: epoch counter (device uint32) required");
   PeerTable pads, xchg;
   if (int rc = fill_table(&pads, pad_ptrs, world)) return rc;
   for (int i = 0; i < kMaxRanks; ++i)
     xchg.p[i] = pads.p[i] ? reinterpret_cast<char*>(pads.p[i]) + kMaxRanks * 4 * 4 : nullptr;
-  allreduce_scalars_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, xchg, rank, world, epoch, in, out, n);
+  allreduce_scalars_kernel<<<1, 32, 0, STREAM(stream)>>>(pads, xchg, rank, world, epoch_counter, in, out, n);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

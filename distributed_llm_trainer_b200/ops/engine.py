@@ -98,8 +98,7 @@ class _Workspace:
             self.dqkv = torch.empty(M, 3 * h, dtype=bf, device=dev)
             self.delta = torch.empty(B, H, S, dtype=f32, device=dev)
             self.dq_acc = torch.empty(M, h, dtype=f32, device=dev)
-        self.graph: Optional[torch.cuda.CUDAGraph] = None
-        self.graph_key = None
+        self.graphs: Dict[tuple, tuple] = {}     # (loss_scale, max_ctas, hooked) -> (CUDAGraph, launches per replay)
         self.calls = 0
 
     def acts_for(self, l: int) -> _LayerActs:
@@ -137,6 +136,8 @@ class FusedGPTEngine:
         self.weights_hook: Optional[Callable[[int], LayerWeights]] = None   # FSDP: gathered weights for layer l
         self.release_hook: Optional[Callable[[int, str], None]] = None      # FSDP: free / reduce after use
         self.grad_ready_hook: Optional[Callable[[int], None]] = None        # DDP: unit's grads are final
+        self.end_step_hook: Optional[Callable[[], None]] = None             # DDP: join forked streams
+        self.hooks_capturable = False     # True when grad_ready_hook/end_step_hook only launch stream-ordered work
         self._bind_views()
 
     # ------------------------------------------------------------------------------------------ parameter views
@@ -311,6 +312,8 @@ class FusedGPTEngine:
         self._lm_head_loss(ws, loss_scale, with_grad=True)
         self._backward_body(ws)
         K.rng_advance(self.rng_state, 1)
+        if self.end_step_hook is not None:
+            self.end_step_hook()
 
     def _load_inputs(self, ws: _Workspace, input_ids: torch.Tensor, labels: Optional[torch.Tensor]) -> None:
         ws.ids.copy_(input_ids.reshape(-1), non_blocking=True)
@@ -325,21 +328,26 @@ class FusedGPTEngine:
         ws = self.workspace(B, S, True)
         self._load_inputs(ws, input_ids, labels)
         ws.calls += 1
-        hooks = self.release_hook is not None or self.grad_ready_hook is not None or self.weights_hook is not None
-        if self.use_graphs and not hooks and ws.calls > 2:
-            key = (float(loss_scale), self.max_ctas)
-            if ws.graph is None or ws.graph_key != key:
+        # FSDP hooks allocate pool slots on the host and cannot be replayed; the DDP gradient hook only forks
+        # kernels onto a second stream (and joins in end_step_hook), which a captured graph records faithfully
+        blocking = (self.release_hook is not None or self.weights_hook is not None
+                    or (self.grad_ready_hook is not None and not self.hooks_capturable))
+        key = (float(loss_scale), self.max_ctas, self.grad_ready_hook is not None)
+        if self.use_graphs and not blocking and ws.calls > 2:
+            entry = ws.graphs.get(key)
+            if entry is None:
                 g = torch.cuda.CUDAGraph()
                 torch.cuda.synchronize()
+                before = K.launch_count
                 with torch.cuda.graph(g):
                     self._step_body(ws, loss_scale)
-                ws.graph, ws.graph_key = g, key
-            ws.graph.replay()
-            K.launch_count += getattr(ws, "graph_launches", 0)
+                entry = (g, K.launch_count - before)
+                K.launch_count = before          # capture recorded the launches, it did not run them
+                ws.graphs[key] = entry
+            entry[0].replay()
+            K.launch_count += entry[1]
         else:
-            before = K.launch_count
             self._step_body(ws, loss_scale)
-            ws.graph_launches = K.launch_count - before
         return ws.loss_sum
 
     # ---- inference ---------------------------------------------------------------------------------------------

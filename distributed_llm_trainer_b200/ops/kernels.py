@@ -56,10 +56,10 @@ _SIGS = {
     "b200_sumsq": [_P, _LL, _LL, _P, _P],
     "b200_clip_coef": [_P, _F, _F, _P, _P, _P],
     "b200_rng_advance": [_P, C.c_ulonglong, _P],
-    "b200_comm_barrier": [_P, _I, _I, _U, _P],
+    "b200_comm_barrier": [_P, _I, _I, _P, _P],
     "b200_reduce_scatter_f32": [_P, _P, _LL, _LL, _F, _P, _I, _I, _I, _P],
     "b200_adamw_bcast": [_P, _P, _P, _P, _P, _I, _I, _P, _LL, _LL, _I, _F, _F, _F, _F, _F, _P, _I, _P],
-    "b200_allreduce_scalars": [_P, _I, _I, _U, _P, _P, _I, _P],
+    "b200_allreduce_scalars": [_P, _I, _I, _P, _P, _P, _I, _P],
     "b200_all_gather_bf16": [_P, _P, _LL, _I, _I, _I, _P],
     "b200_reduce_scatter_bf16_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
     "b200_reduce_scatter_f32_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
@@ -241,8 +241,8 @@ def ptr_array(ptrs):
     return (C.c_void_p * len(ptrs))(*ptrs)
 
 
-def comm_barrier(pad_ptrs, rank, world, epoch):
-    _call("b200_comm_barrier", pad_ptrs, rank, world, epoch & 0xFFFFFFFF, _stream())
+def comm_barrier(pad_ptrs, rank, world, epoch_counter):
+    _call("b200_comm_barrier", pad_ptrs, rank, world, epoch_counter.data_ptr(), _stream())
 
 
 def reduce_scatter_f32(grad_ptrs, dst, lo, hi, scale, sumsq, rank, world, max_ctas=0):
@@ -257,8 +257,8 @@ def adamw_bcast(master, grad, exp_avg, exp_avg_sq, shadow_ptrs, rank, world, dec
           _ptr(grad_scale), max_ctas, _stream())
 
 
-def allreduce_scalars(pad_ptrs, rank, world, epoch, inp, out, n):
-    _call("b200_allreduce_scalars", pad_ptrs, rank, world, epoch & 0xFFFFFFFF, inp.data_ptr(), out.data_ptr(), n,
+def allreduce_scalars(pad_ptrs, rank, world, epoch_counter, inp, out, n):
+    _call("b200_allreduce_scalars", pad_ptrs, rank, world, epoch_counter.data_ptr(), inp.data_ptr(), out.data_ptr(), n,
           _stream())
 
 

@@ -84,21 +84,21 @@ class SymmetricBuffer:
 
 
 class SignalPads:
-    """Per-rank flag area + the monotonically increasing epoch every waiting kernel is launched with."""
+    """Per-rank flag area + the epoch counter of pad operations.
+
+    The counter lives in device memory and is bumped by the pad kernels themselves, so barrier /
+    scalar-all-reduce launches carry no changing host argument and can sit inside a captured CUDA graph.
+    Invariant: all ranks issue the same sequence of pad operations, and never on two streams at once."""
 
     def __init__(self, device: torch.device, group=None):
         nbytes = _lib.lib().b200_comm_pad_bytes()
         self.buf = SymmetricBuffer(nbytes // 4, torch.int32, device, group)
         self.rank, self.world = self.buf.rank, self.buf.world
-        self.epoch = 0
-
-    def next_epoch(self) -> int:
-        self.epoch += 1
-        return self.epoch
+        self.counter = torch.zeros(1, dtype=torch.int32, device=device)
 
     def barrier(self) -> None:
         """Device-side barrier on the current stream (no host sync)."""
-        K.comm_barrier(self.buf.ptrs, self.rank, self.world, self.next_epoch())
+        K.comm_barrier(self.buf.ptrs, self.rank, self.world, self.counter)
 
     def allreduce_scalars(self, inp: torch.Tensor, out: torch.Tensor, n: int) -> None:
-        K.allreduce_scalars(self.buf.ptrs, self.rank, self.world, self.next_epoch(), inp, out, n)
+        K.allreduce_scalars(self.buf.ptrs, self.rank, self.world, self.counter, inp, out, n)

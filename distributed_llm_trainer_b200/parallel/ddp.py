@@ -144,6 +144,8 @@ class NVLinkGradSync:
             self.sumsq.zero_()
             self._units_done = 0
             self.engine.grad_ready_hook = self._on_unit_ready
+            self.engine.end_step_hook = self._join_comm
+            self.engine.hooks_capturable = True
             self._overlapped = True
 
     def _on_unit_ready(self, unit: int) -> None:
@@ -160,6 +162,11 @@ class NVLinkGradSync:
                                  self.rank, self.world, self.comm_ctas)
         self._units_done += 1
 
+    def _join_comm(self) -> None:
+        """End of the micro-step: the compute stream waits for the forked reductions (inside a CUDA graph
+        capture this is the join that closes the fork)."""
+        torch.cuda.current_stream().wait_stream(self.comm_stream)
+
     # ---- the fused step --------------------------------------------------------------------------------
     def finish_and_step(self, grad_clip: float, norm_out: Optional[torch.Tensor] = None) -> None:
         from ..ops import kernels as K
@@ -169,9 +176,9 @@ class NVLinkGradSync:
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
         opt.step_count += 1
         if self._overlapped:
-            assert self._units_done == len(self.ranges), "a unit never reported its gradients"
+            # reductions were forked under the backward and already joined by end_step_hook
             self.engine.grad_ready_hook = None
-            torch.cuda.current_stream().wait_stream(self.comm_stream)
+            self.engine.end_step_hook = None
         else:
             self.sumsq.zero_()
             # every rank's backward has finished writing its gradients
@@ -248,6 +255,12 @@ def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, s
     store.refresh_shadow()
     eng = FusedGPTEngine(model, store=store, seed=seed)
     sync = NVLinkGradSync(eng, rank, world_size, grad_buf, shadow_buf, pads)
+    # first launches of the comm kernels happen here, eagerly, not inside a later CUDA-graph capture
+    from ..ops import kernels as K
+
+    pads.barrier()
+    K.reduce_scatter_f32(grad_buf.ptrs, store.grad, 0, 128, 1.0, sync.sumsq[0:1], rank, world_size, 1)
+    pads.barrier()
     torch.cuda.synchronize()
     dist.barrier()
     return eng, sync

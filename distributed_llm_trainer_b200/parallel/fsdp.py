@@ -219,6 +219,8 @@ class ShardedGPT:
         e._ws = {}
         e.use_graphs = False
         e.fuse_swiglu_bwd = True
+        e.end_step_hook = None
+        e.hooks_capturable = False
         e.max_ctas = 0
         e.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self._LayerWeights = LayerWeights

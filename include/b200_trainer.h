@@ -175,11 +175,13 @@ int b200_rng_advance(unsigned long long* rng_state, unsigned long long delta, vo
 /* ---------------------------------------------------------------- NVLink communication -------- */
 /* All of these take HOST arrays of `world` device pointers (one per rank, index = rank), each pointing
  * at that rank's copy of a symmetric buffer mapped into this process (b200_ipc_open).  `pad_ptrs` are
- * the signal pads (b200_comm_pad_bytes() bytes each, zero-initialised).  `epoch` must increase by one
- * on every call that takes it, identically on all ranks.  Kernels that wait on peers are bounded by a
- * 20 s device-side timeout and trap instead of hanging. */
+ * the signal pads (b200_comm_pad_bytes() bytes each, zero-initialised).  `epoch_counter` is a zero-initialised
+ * uint32 in THIS rank's device memory that the pad kernels bump themselves (so launches carry no changing
+ * host argument and can be captured in CUDA graphs); every rank must issue the same sequence of pad
+ * operations and never have two of them in flight on different streams.  Kernels that wait on peers are
+ * bounded by a 20 s device-side timeout and trap instead of hanging. */
 int b200_comm_pad_bytes(void);
-int b200_comm_barrier(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, void* stream);
+int b200_comm_barrier(const void* const* pad_ptrs, int rank, int world, unsigned int* epoch_counter, void* stream);
 /* dst[lo:hi] = scale * sum_r grads_r[lo:hi]; sumsq[0] += |dst[lo:hi]|^2  (reference: DDP bucket all-reduce
  * ddp_trainer.py:342 + clip_grad_norm_ :350, FSDP reduce_scatter fsdp_trainer.py:383) */
 int b200_reduce_scatter_f32(const void* const* grad_ptrs, float* dst, long long lo, long long hi, float scale,
@@ -191,8 +193,8 @@ int b200_adamw_bcast(float* master, const float* grad, float* exp_avg, float* ex
                      long long hi, int step, float lr, float beta1, float beta2, float eps, float weight_decay,
                      const float* grad_scale, int max_ctas, void* stream);
 /* out[i] = sum_r in_r[i], i < n <= 8 (reference: FSDP.clip_grad_norm_ scalar all-reduce, fsdp_trainer.py:388) */
-int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, unsigned int epoch, const float* in,
-                           float* out, int n, void* stream);
+int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, unsigned int* epoch_counter,
+                           const float* in, float* out, int n, void* stream);
 /* dst[r*shard + i] = shard_r[i]  (reference: FSDP all_gather_into_tensor, fsdp_trainer.py:379,383) */
 int b200_all_gather_bf16(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
                          int max_ctas, void* stream);

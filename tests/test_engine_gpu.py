@@ -100,7 +100,7 @@ def test_engine_graph_replay_and_dropout_determinism():
         eng.use_graphs = graphs
         eng.set_seed(7)
         for ws in eng._ws.values():
-            ws.calls, ws.graph = 0, None
+            ws.calls, ws.graphs = 0, {}
         eng.store.zero_grad()
         losses = []
         for _ in range(n):
