@@ -120,9 +120,13 @@ class NVLinkGradSync:
         self.optimizer = None
         self.comm_stream = torch.cuda.Stream(device=dev)
         self.max_ctas = 0
-        # fork per-unit reductions under the last backward (B200_DDP_OVERLAP=0: reduce everything after it)
-        self.overlap = __import__("os").environ.get("B200_DDP_OVERLAP", "1") != "0"
-        self.comm_ctas = 32          # small grid: shares the SMs with the backward GEMMs it overlaps
+        # B200_DDP_OVERLAP=1 forks per-unit reductions under the last backward (captured in the CUDA graph of
+        # that micro-step).  Default off: measured on 2xB200 with the small model the whole reduction is ~0.5 ms
+        # of a 52 ms step, and running it under the backward GEMMs costs them more (52.8 ms with overlap and 32
+        # comm CTAs, 62.4 ms with 4, vs 51.7 ms reducing after the backward) -- profiles/ddp_overlap_ab.md.
+        self.overlap = __import__("os").environ.get("B200_DDP_OVERLAP", "0") == "1"
+        # small grid: shares the SMs with the backward GEMMs it overlaps
+        self.comm_ctas = int(__import__("os").environ.get("B200_DDP_COMM_CTAS", "32"))
         self._last = False
         self._overlapped = False
         self._units_done = 0
