@@ -65,7 +65,36 @@ struct Params {
   const unsigned long long* rng;
   unsigned int rng_stream;
   int half_n;
+  // ---- all-gather fused into the GEMM (AG instantiations): B is a weight sharded across ranks -------------
+  const void* ag_src[16];      // every rank's bf16 shard of the unit that contains B (peer-mapped)
+  void* ag_dst;                // local gathered copy of B ([N, K] bf16, contiguous) = what the B tensor map reads
+  long long ag_part;           // elements of the unit owned by each rank
+  long long ag_b_off;          // element offset of B inside the unit
+  unsigned int* ag_flags;      // local, one per 128-row block of B: == ag_epoch once the block has landed
+  unsigned int ag_epoch;
+  int ag_pairs;                // CTA pairs that gather instead of multiplying
+  int ag_rot;                  // n-tile rotation so tiles over locally owned rows are visited first
+  int ag_rank, ag_world;
 };
+
+__device__ __forceinline__ void bulk_load_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_dst),
+               "l"(reinterpret_cast<uint64_t>(gsrc)), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void bulk_store_s2g(void* gdst, uint32_t smem_src, uint32_t bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(reinterpret_cast<uint64_t>(gdst)),
+               "r"(smem_src), "r"(bytes)
+               : "memory");
+}
+__device__ __forceinline__ uint32_t ld_acquire_gpu_u32(const unsigned int* p) {
+  uint32_t v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ void st_release_gpu_u32(unsigned int* p, uint32_t v) {
+  asm volatile("st.release.gpu.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
 
 __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   uint4 v;
@@ -76,7 +105,7 @@ __device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.0f, 1.
 
 // tma_c: primary output.  tma_x: second tensor -- RESID_DROPOUT: residual (fp32, input); SWIGLU: act (bf16,
 // output); SWIGLU_BWD: saved [gate|up] (bf16, input).
-template <int BNP, bool A_MN, bool B_MN, int EPI>
+template <int BNP, bool A_MN, bool B_MN, int EPI, bool AG = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
              const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p) {
@@ -99,10 +128,21 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const uint32_t cta_rank = cluster_ctarank();
   const bool leader = cta_rank == 0;
-  const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+  // AG: the first ag_pairs pairs of the grid are gather CTAs (pair < 0 below); the rest multiply
+  const int ag_pairs = AG ? p.ag_pairs : 0;
+  const int pair = int(blockIdx.x >> 1) - ag_pairs, npairs = int(gridDim.x >> 1) - ag_pairs;
 
   const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int tiles_n = (p.N + BNP - 1) / BNP;
+  // n-tile of linear tile index r (m fastest).  AG rotates the n order so locally owned weight rows come first.
+  auto ntile = [&](int r) {
+    int qn = r / tiles_m;
+    if constexpr (AG) {
+      qn += p.ag_rot;
+      if (qn >= tiles_n) qn -= tiles_n;
+    }
+    return qn;
+  };
   const int tiles_mn = tiles_m * tiles_n;
   const int num_tiles = tiles_mn * p.split_k;
   const int k_blocks_total = (p.K + BK - 1) / BK;
@@ -130,7 +170,62 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   tc_fence_after();
   const uint32_t tmem_base = *tmem_ptr;
 
-  if (warp == 0) {
+  if (AG && pair < 0) {
+    // ------------------------------------------------------------------ gather CTAs (fused all-gather)
+    // One thread per CTA streams 128-row blocks of the weight from their owners' shards (peer memory over
+    // NVLink, or the local shard) through a ring of 32 KB smem slots with bulk async copies
+    // (peer -> smem -> local gathered buffer), then publishes the block's flag.  Blocks are taken round-robin
+    // by the gather CTAs, starting at the locally owned rows -- the order the GEMM pairs consume them in.
+    if constexpr (AG) if (threadIdx.x == 0) {
+      constexpr int NS = 5;                       // ring depth: 5 x 32 KB (the GEMM's operand stages, unused here)
+      constexpr long long CH = 16384;             // elements per chunk (32 KB)
+      static_assert(NS * CH * 2 <= kStages * C::kStage, "gather ring does not fit in the operand stages");
+      const int gi = blockIdx.x, GC = 2 * ag_pairs;
+      const int nblocks = (p.N + 127) / 128;
+      const int first = p.ag_rot * (BNP / 128);   // first row block the GEMM pairs will ask for
+      const long long blk_elems = 128LL * p.K;
+      const long long b_total = (long long)p.N * p.K;
+      const __nv_bfloat16* const* srcs = reinterpret_cast<const __nv_bfloat16* const*>(p.ag_src);
+      __nv_bfloat16* dst = reinterpret_cast<__nv_bfloat16*>(p.ag_dst);
+      uint32_t G = 0;                             // running chunk counter: ring slot and mbarrier phase
+      for (int k = gi; k < nblocks; k += GC) {
+        int nb = first + k;
+        if (nb >= nblocks) nb -= nblocks;
+        const long long b0 = nb * blk_elems;                               // element offset inside B
+        const long long total = min(blk_elems, b_total - b0);
+        const int n = int((total + CH - 1) / CH);
+        const uint32_t Gbase = G;
+        for (int i = 0; i < n + (NS - 2); ++i) {
+          if (i < n) {
+            if (i >= NS) tma_store_wait_read<1>();   // the store that last read this slot has finished with it
+            const uint32_t slot = (Gbase + i) % NS;
+            const long long off = b0 + i * CH, len = min(CH, total - i * CH);
+            const long long u0 = p.ag_b_off + off;                           // element offset inside the unit
+            const int owner = int(u0 / p.ag_part);
+            const long long in_owner = min(len, (owner + 1) * p.ag_part - u0);
+            uint64_t* bar = &full_bar[slot];
+            mbar_expect_tx(bar, uint32_t(len * 2));
+            const uint32_t sdst = smem_u32(smem_a + slot * (CH * 2));
+            bulk_load_g2s(sdst, srcs[owner] + (u0 - owner * p.ag_part), uint32_t(in_owner * 2), bar);
+            if (in_owner < len)   // chunk straddles two owners
+              bulk_load_g2s(sdst + uint32_t(in_owner * 2), srcs[owner + 1], uint32_t((len - in_owner) * 2), bar);
+          }
+          const int d = i - (NS - 2);
+          if (d >= 0 && d < n) {
+            const uint32_t gd = Gbase + d, slot = gd % NS;
+            mbar_wait(&full_bar[slot], (gd / NS) & 1);
+            const long long off = b0 + d * CH, len = min(CH, total - d * CH);
+            bulk_store_s2g(dst + off, smem_u32(smem_a + slot * (CH * 2)), uint32_t(len * 2));
+            tma_store_commit();
+          }
+        }
+        G = Gbase + n;
+        tma_store_wait<0>();        // every byte of this block has been written
+        __threadfence();
+        st_release_gpu_u32(p.ag_flags + nb, p.ag_epoch);
+      }
+    }
+  } else if (warp == 0) {
     // ------------------------------------------------------------------ TMA producer (both CTAs)
     if (lane == 0) {
       int stage = 0;
@@ -139,11 +234,26 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         const int ks = t / tiles_mn;
         const int r = t - ks * tiles_mn;
         const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;   // this CTA's rows
-        const int nt = (r / tiles_m) * BNP;
+        const int nt = ntile(r) * BNP;
         // this CTA's half of the B tile; SwiGLU: leader stages gate rows, peer the matching up rows
         const int n0 = (EPI == EPI_SWIGLU) ? (cta_rank == 0 ? nt / 2 : p.half_n + nt / 2) : nt + int(cta_rank) * C::BNH;
         const int kb0 = ks * p.k_per_split;
         const int kb1 = min(k_blocks_total, kb0 + p.k_per_split);
+        if constexpr (AG) {
+          // the 128 weight rows this CTA is about to stage must have arrived from their owners
+          if (n0 < p.N) {
+            const unsigned int* flag = p.ag_flags + n0 / 128;
+            const unsigned long long t0 = global_timer_ns();
+            uint32_t spins = 0;
+            while (ld_acquire_gpu_u32(flag) != p.ag_epoch) {
+              if ((++spins & 0xFF) == 0 && global_timer_ns() - t0 > B200_WAIT_TIMEOUT_NS) {
+                printf("b200: fused all-gather GEMM timed out waiting for weight rows %d (block %d)\n", n0, blockIdx.x);
+                __trap();
+              }
+            }
+            asm volatile("fence.proxy.async;" ::: "memory");   // bulk-store writes -> visible to this TMA read
+          }
+        }
         for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty_bar[stage], phase ^ 1);
           if (leader) mbar_expect_tx(&full_bar[stage], 2 * C::kStage);   // bytes of both CTAs land on this barrier
@@ -225,7 +335,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       const int t = pair + it * npairs;
       const int r = t % tiles_mn;
       m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
-      n0 = (r / tiles_m) * BNP;
+      n0 = ntile(r) * BNP;
     };
     uint32_t g = 0;   // store-only staging ring position
     auto stage_begin = [&]() -> uint32_t {
@@ -291,7 +401,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       const int t = pair + it * npairs;
       const int r = t % tiles_mn;
       const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
-      const int n0 = (r / tiles_m) * BNP;
+      const int n0 = ntile(r) * BNP;
       const int row = m0 + r_in;
       const int buf = it & 1;
       const uint32_t buf_phase = (it >> 1) & 1;
@@ -497,10 +607,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   }
 }
 
-template <int BNP, bool A_MN, bool B_MN, int EPI>
+template <int BNP, bool A_MN, bool B_MN, int EPI, bool AG = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
                   const Params& p, int grid, cudaStream_t stream) {
-  auto kfn = gemm2_kernel<BNP, A_MN, B_MN, EPI>;
+  auto kfn = gemm2_kernel<BNP, A_MN, B_MN, EPI, AG>;
   static bool configured = false;
   if (!configured) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BNP, EPI>::kSmemTotal));
@@ -544,7 +654,16 @@ static int dispatch_epi(int epi, bool a_mn, bool b_mn, const CUtensorMap& ta, co
 
 using namespace b200;
 
-extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) {
+static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stream_);
+
+extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) { return run_gemm2(a, nullptr, stream_); }
+
+extern "C" int b200_gemm2_ag_bf16(const b200_gemm_args* a, const b200_ag_args* ag, void* stream_) {
+  B200_REQUIRE(ag != nullptr, "gemm2_ag: null all-gather arguments");
+  return run_gemm2(a, ag, stream_);
+}
+
+static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stream_) {
   using namespace b200::g2;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   B200_REQUIRE(a != nullptr, "gemm2: null args");
@@ -604,6 +723,37 @@ extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) {
   long pairs = sms / 2;
   if (pairs < 1) pairs = 1;
   if (tiles < pairs) pairs = tiles;
+  if (ag != nullptr) {
+    // all-gather fused into the GEMM: some pairs gather the weight rows over NVLink, the others multiply
+    B200_REQUIRE(epi == EPI_BF16 || epi == EPI_ROPE_BF16, "gemm2_ag: epilogue %d is not instantiated with the fused gather", epi);
+    B200_REQUIRE(!a_mn && !b_mn && bnp == 256 && p.split_k == 1, "gemm2_ag: needs K-major operands, the 256-wide tile, no split-K");
+    B200_REQUIRE(a->ldb == a->K, "gemm2_ag: the gathered B must be contiguous (ldb == K)");
+    B200_REQUIRE(ag->world >= 1 && ag->world <= 16 && ag->rank >= 0 && ag->rank < ag->world, "gemm2_ag: bad rank/world");
+    B200_REQUIRE(ag->part_elems >= 16384 && ag->part_elems % 8 == 0 && ag->b_offset_elems % 8 == 0,
+                 "gemm2_ag: shard size must be >= 16384 elements and 16-byte aligned");
+    B200_REQUIRE(ag->b_offset_elems + (long long)a->N * a->K <= ag->part_elems * ag->world, "gemm2_ag: B lies outside the unit");
+    B200_REQUIRE(ag->flags != nullptr && ag->shard_ptrs != nullptr, "gemm2_ag: flags / shard pointers missing");
+    int gp = ag->gather_pairs > 0 ? ag->gather_pairs : 4;
+    const int hw_pairs = sms / 2;
+    if (gp > hw_pairs - 1) gp = hw_pairs - 1;
+    B200_REQUIRE(gp >= 1, "gemm2_ag: not enough SMs for a gather pair");
+    long gemm_pairs = hw_pairs - gp;
+    if (tiles < gemm_pairs) gemm_pairs = tiles;
+    for (int i = 0; i < 16; ++i) p.ag_src[i] = i < ag->world ? ag->shard_ptrs[i] : nullptr;
+    p.ag_dst = const_cast<void*>(a->B);
+    p.ag_part = ag->part_elems; p.ag_b_off = ag->b_offset_elems; p.ag_flags = ag->flags; p.ag_epoch = ag->epoch;
+    p.ag_pairs = gp; p.ag_rank = ag->rank; p.ag_world = ag->world;
+    // first n-tile that contains a locally owned weight row
+    long long first_local = ag->rank * ag->part_elems - ag->b_offset_elems;
+    if (first_local < 0) first_local = 0;
+    const int tiles_n = (a->N + 255) / 256;
+    int rot = int((first_local / a->K) / 256);
+    if (rot >= tiles_n) rot = 0;
+    p.ag_rot = rot;
+    const int ag_grid = int((gp + gemm_pairs) * 2);
+    if (epi == EPI_BF16) return launch<256, false, false, EPI_BF16, true>(ta, tb, tc, tx, p, ag_grid, stream);
+    return launch<256, false, false, EPI_ROPE_BF16, true>(ta, tb, tc, tx, p, ag_grid, stream);
+  }
   const int grid = int(pairs * 2);
   if (epi == EPI_SWIGLU) return dispatch<256, EPI_SWIGLU>(a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
   if (bnp == 256) return dispatch_epi<256>(epi, a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);

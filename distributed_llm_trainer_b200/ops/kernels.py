@@ -34,8 +34,17 @@ class GemmArgs(C.Structure):
     ]
 
 
+class AgArgs(C.Structure):
+    """``b200_ag_args``: where the rows of a sharded weight live on every rank (fused all-gather GEMM)."""
+    _fields_ = [
+        ("shard_ptrs", C.c_void_p), ("part_elems", C.c_longlong), ("b_offset_elems", C.c_longlong),
+        ("flags", C.c_void_p), ("epoch", C.c_uint), ("rank", C.c_int), ("world", C.c_int), ("gather_pairs", C.c_int),
+    ]
+
+
 _P, _I, _F, _LL, _U = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint
 _SIGS = {
+    "b200_gemm2_ag_bf16": [C.POINTER(GemmArgs), C.POINTER(AgArgs), _P],
     "b200_gemm_bf16": [C.POINTER(GemmArgs), _P],
     "b200_gemm2_bf16": [C.POINTER(GemmArgs), _P],
     "b200_embed_fwd": [_P, _P, _P, _I, _I, _I, _P],
@@ -99,7 +108,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
          rope_cos=None, rope_sin=None, seq_len: int = 0, rope_cols: int = 0,
          residual=None, dropout_p: float = 0.0, rng_state=None, rng_stream: int = 0,
          aux=None, half_n: int = 0, M: Optional[int] = None, N: Optional[int] = None, K: Optional[int] = None,
-         pair: Optional[bool] = None) -> None:
+         pair: Optional[bool] = None, ag=None) -> None:
     """``c = a @ b`` on tcgen05.  ``pair=True`` selects the CTA-pair kernel (``cta_group::2``, 256x256 tiles,
     TMA-store epilogue); ``None`` lets ``use_pair_kernel`` decide for the epilogues that kernel implements.
 
@@ -122,6 +131,14 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
         residual=_ptr(residual), dropout_p=dropout_p, rng_state=_ptr(rng_state), rng_stream=rng_stream,
         aux=_ptr(aux), ld_aux=0 if aux is None else aux.stride(0), half_n=half_n,
     )
+    if ag is not None:
+        # all-gather fused into the GEMM: ``b`` is the local gathered destination the kernel fills while it multiplies
+        shard_ptrs, part_elems, b_offset_elems, flags, epoch, rank, world, gather_pairs = ag
+        agargs = AgArgs(shard_ptrs=C.cast(shard_ptrs, C.c_void_p), part_elems=part_elems, b_offset_elems=b_offset_elems,
+                        flags=flags.data_ptr(), epoch=epoch & 0xFFFFFFFF, rank=rank, world=world,
+                        gather_pairs=gather_pairs)
+        _call("b200_gemm2_ag_bf16", C.byref(args), C.byref(agargs), _stream())
+        return
     if pair is None:
         pair = (use_pair_kernel and M >= 256 and N >= 128 and not (a_mn and epilogue > EPI_F32_ATOMIC)
                 and not (epilogue == EPI_SWIGLU and (half_n % 128 or b_mn)))

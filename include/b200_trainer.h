@@ -80,6 +80,24 @@ int b200_gemm_bf16(const b200_gemm_args* args, void* stream);
  * _F32_ATOMIC; C row pitch must be a multiple of 16 bytes.  Same reference ops as b200_gemm_bf16. */
 int b200_gemm2_bf16(const b200_gemm_args* args, void* stream);
 
+/* All-gather fused into the consuming GEMM (FSDP: the QKV projection is the first consumer of a block's
+ * weights; reference: FSDP1 all_gather_into_tensor before the block forward, fsdp_trainer.py:379).  B is a
+ * weight whose rows are sharded across ranks: inside ONE launch, `gather_pairs` CTA pairs stream the 128-row
+ * blocks of B from their owners' shards (peer memory over NVLink) into args->B with bulk async copies and
+ * publish a per-block flag, while the remaining pairs run the tcgen05 GEMM, their TMA producers waiting on
+ * the flag of the rows they stage; tiles over locally owned rows are visited first, so the transfer overlaps
+ * the math tile by tile.  Epilogues: B200_EPI_BF16, B200_EPI_ROPE_BF16.  K-major operands, ldb == K. */
+typedef struct b200_ag_args {
+  const void* const* shard_ptrs; /* host array [world]: every rank's bf16 shard of the unit (device pointers) */
+  long long part_elems;          /* elements of the unit owned by each rank (rank r owns [r*part, (r+1)*part)) */
+  long long b_offset_elems;      /* offset of B inside the unit */
+  unsigned int* flags;           /* device uint32[ceil(N/128)]; must not already hold `epoch` */
+  unsigned int epoch;            /* value published per block: use a new one for every call that reuses flags */
+  int rank, world;
+  int gather_pairs;              /* 0 = default (4 pairs = 8 SMs) */
+} b200_ag_args;
+int b200_gemm2_ag_bf16(const b200_gemm_args* args, const b200_ag_args* ag, void* stream);
+
 /* ---------------------------------------------------------------- normalisation / elementwise */
 /* Token embedding gather into the fp32 residual stream (reference gpt.py:438). ids: int64 [rows]. */
 int b200_embed_fwd(const int64_t* ids, const void* weight_bf16, float* out, int rows, int hidden, int vocab,

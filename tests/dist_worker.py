@@ -247,18 +247,69 @@ def mode_comm(tmp):
         b.close()
 
 
+def mode_aggemm(tmp):
+    """All-gather fused into the GEMM: every rank owns a slice of a 'unit' that contains the weight; one launch
+    gathers the weight rows over NVLink while it multiplies.  Checked against a plain matmul on the full weight."""
+    from distributed_llm_trainer_b200.ops import kernels as K
+    from distributed_llm_trainer_b200.ops import reference as R
+    from distributed_llm_trainer_b200.parallel.comm import SignalPads, SymmetricBuffer
+
+    local = int(os.environ["LOCAL_RANK"])
+    dev = torch.device(f"cuda:{local}")
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    pads = SignalPads(dev)
+    N, Kd, M, S = 1536, 512, 2048, 256
+    b_off = 4096 + 128 * 3                      # the weight does not start on a shard boundary
+    unit = b_off + N * Kd + 1000
+    part = ((unit + world - 1) // world + 127) // 128 * 128
+    part = max(part, 16384)
+    torch.manual_seed(1234)                      # same full unit on every rank; each keeps only its slice
+    full = (torch.randn(part * world) * 0.05).to(torch.bfloat16)
+    shard = SymmetricBuffer(part, torch.bfloat16, dev)
+    shard.local.copy_(full[rank * part:(rank + 1) * part])
+    w_ref = full[b_off: b_off + N * Kd].view(N, Kd).to(dev)
+    x = (torch.randn(M, Kd, device=dev)).to(torch.bfloat16)
+    flags = torch.zeros((N + 127) // 128, dtype=torch.int32, device=dev)
+    cos, sin = R.rope_tables(S, 64, device=dev)
+    pads.barrier()
+    torch.cuda.synchronize()
+    for epoch, epi in ((1, K.EPI_BF16), (2, K.EPI_ROPE_BF16), (3, K.EPI_BF16)):
+        gathered = torch.zeros(N, Kd, dtype=torch.bfloat16, device=dev)      # nothing local to start from
+        out = torch.full((M, N), float("nan"), dtype=torch.bfloat16, device=dev)
+        kw = dict(rope_cos=cos, rope_sin=sin, seq_len=S, rope_cols=1024) if epi == K.EPI_ROPE_BF16 else {}
+        K.gemm(x, gathered, out, epilogue=epi, ag=(shard.ptrs, part, b_off, flags, epoch, rank, world, 2 + epoch % 2), **kw)
+        torch.cuda.synchronize()
+        assert torch.equal(gathered, w_ref), f"epoch {epoch}: gathered weight differs from the owners' rows"
+        ref = x.float() @ w_ref.float().t()
+        if epi == K.EPI_ROPE_BF16:
+            ref = R.rope_packed(ref, cos, sin, S, 1024)
+        close(out, ref, 2e-2, f"fused all-gather GEMM (epoch {epoch})")
+        assert int(flags.min().item()) == epoch
+    pads.barrier()
+    torch.cuda.synchronize()
+    dist.barrier()
+    shard.close()
+    pads.buf.close()
+
+
 def main():
     mode = sys.argv[1]
     tmp = sys.argv[2] if len(sys.argv) > 2 else "/tmp/b200_dist_test"
     os.makedirs(tmp, exist_ok=True)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    if mode == "ddp":
+    if mode in ("ddp", "ddp:overlap"):
+        if mode == "ddp:overlap":
+            os.environ["B200_DDP_OVERLAP"] = "1"    # fork the per-unit reductions under the last backward
         mode_ddp(tmp)
     elif mode.startswith("fsdp"):
         parts = mode.split(":")
         mode_fsdp(tmp, parts[1], offload=len(parts) > 2 and parts[2] == "offload")
     elif mode == "comm":
         mode_comm(tmp)
+    elif mode == "aggemm":
+        mode_aggemm(tmp)
     else:
         raise SystemExit(f"unknown mode {mode}")
     if dist.is_initialized():
