@@ -217,13 +217,18 @@ __global__ void allreduce_scalars_kernel(PeerTable pads, PeerTable xchg, int ran
 
 // dst[r * shard + i] = src_r[i]   (pull every peer's shard into the local full buffer), 16 B units
 __global__ void __launch_bounds__(512)
-all_gather_pull_kernel(PeerTable srcs, uint4* __restrict__ dst, long long shard16, int rank, int world) {
+all_gather_pull_kernel(PeerTable srcs, uint4* __restrict__ dst, long long shard16, int rank, int world,
+                       long long excl_lo16, long long excl_hi16) {
+  // [excl_lo16, excl_hi16): 16-byte units of the gathered buffer that somebody else fills (the fused
+  // all-gather GEMM gathers the rows of its own weight) and this kernel must leave alone
   const long long total = shard16 * world;
   for (long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x; i < total; i += (long long)gridDim.x * blockDim.x) {
     const int rr = int(i / shard16);
     const int r = (rank + rr) % world;
     const long long off = i - rr * shard16;
-    dst[r * shard16 + off] = ld_peer_u4(reinterpret_cast<const uint4*>(srcs.p[r]) + off);
+    const long long pos = r * shard16 + off;
+    if (pos >= excl_lo16 && pos < excl_hi16) continue;
+    dst[pos] = ld_peer_u4(reinterpret_cast<const uint4*>(srcs.p[r]) + off);
   }
 }
 
@@ -352,7 +357,14 @@ int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, uns
 
 int b200_all_gather_bf16(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
                          int max_ctas, void* stream) {
+  return b200_all_gather_bf16_excl(shard_ptrs, dst, shard_elems, rank, world, 0, 0, max_ctas, stream);
+}
+
+int b200_all_gather_bf16_excl(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
+                              long long excl_lo_elems, long long excl_hi_elems, int max_ctas, void* stream) {
   B200_REQUIRE(shard_elems % 8 == 0, "all_gather: shard must be a multiple of 8 bf16 elements");
+  B200_REQUIRE(excl_lo_elems % 8 == 0 && excl_hi_elems % 8 == 0 && excl_hi_elems >= excl_lo_elems,
+               "all_gather: excluded window must be 8-element aligned");
   PeerTable srcs;
   if (int rc = fill_table(&srcs, shard_ptrs, world)) return rc;
   const long long shard16 = shard_elems / 8;
@@ -360,7 +372,8 @@ int b200_all_gather_bf16(const void* const* shard_ptrs, void* dst, long long sha
   const long long cap = max_ctas > 0 ? max_ctas : (long long)sm_count() * 2;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
-  all_gather_pull_kernel<<<(unsigned)blocks, 512, 0, STREAM(stream)>>>(srcs, (uint4*)dst, shard16, rank, world);
+  all_gather_pull_kernel<<<(unsigned)blocks, 512, 0, STREAM(stream)>>>(srcs, (uint4*)dst, shard16, rank, world,
+                                                                      excl_lo_elems / 8, excl_hi_elems / 8);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -137,6 +137,7 @@ class FusedGPTEngine:
         self.release_hook: Optional[Callable[[int, str], None]] = None      # FSDP: free / reduce after use
         self.grad_ready_hook: Optional[Callable[[int], None]] = None        # DDP: unit's grads are final
         self.end_step_hook: Optional[Callable[[], None]] = None             # DDP: join forked streams
+        self.ag_hook: Optional[Callable[[int], Optional[tuple]]] = None     # FSDP: fused all-gather args for QKV
         self.hooks_capturable = False     # True when grad_ready_hook/end_step_hook only launch stream-ordered work
         self._bind_views()
 
@@ -205,8 +206,11 @@ class FusedGPTEngine:
         p_att = cfg.attention_dropout if train else 0.0
         rng = self.rng_state
         K.rmsnorm_fwd(x_in, W.ln1, a.xn1, a.rstd1, 1e-6)
+        # FSDP: the QKV projection is the first consumer of a block's gathered weights -- its launch also
+        # gathers the q|k|v rows from the peers (all-gather fused into the GEMM) when ag_hook says so
+        ag = self.ag_hook(l) if self.ag_hook is not None else None
         K.gemm(a.xn1, W.wqkv, a.qkv, epilogue=K.EPI_ROPE_BF16, rope_cos=self.rope_cos, rope_sin=self.rope_sin,
-               seq_len=ws.S, rope_cols=2 * h, max_ctas=self.max_ctas)
+               seq_len=ws.S, rope_cols=2 * h, max_ctas=self.max_ctas, ag=ag)
         K.attn_fwd(a.qkv, a.attn, a.lse, ws.B, ws.S, cfg.num_heads, p_att, rng, 8 * l)
         K.gemm(a.attn, W.wo, a.xmid, epilogue=K.EPI_RESID_DROPOUT, residual=x_in, dropout_p=p_res, rng_state=rng,
                rng_stream=8 * l + 1, max_ctas=self.max_ctas)

@@ -70,6 +70,7 @@ _SIGS = {
     "b200_adamw_bcast": [_P, _P, _P, _P, _P, _I, _I, _P, _LL, _LL, _I, _F, _F, _F, _F, _F, _P, _I, _P],
     "b200_allreduce_scalars": [_P, _I, _I, _P, _P, _P, _I, _P],
     "b200_all_gather_bf16": [_P, _P, _LL, _I, _I, _I, _P],
+    "b200_all_gather_bf16_excl": [_P, _P, _LL, _I, _I, _LL, _LL, _I, _P],
     "b200_reduce_scatter_bf16_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
     "b200_reduce_scatter_f32_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
 }
@@ -279,8 +280,10 @@ def allreduce_scalars(pad_ptrs, rank, world, epoch_counter, inp, out, n):
           _stream())
 
 
-def all_gather_bf16(shard_ptrs, dst, shard_elems, rank, world, max_ctas=0):
-    _call("b200_all_gather_bf16", shard_ptrs, dst.data_ptr(), shard_elems, rank, world, max_ctas, _stream())
+def all_gather_bf16(shard_ptrs, dst, shard_elems, rank, world, max_ctas=0, exclude=(0, 0)):
+    """``exclude=(lo, hi)``: elements of ``dst`` to leave alone (filled by a fused all-gather GEMM instead)."""
+    _call("b200_all_gather_bf16_excl", shard_ptrs, dst.data_ptr(), shard_elems, rank, world, exclude[0], exclude[1],
+          max_ctas, _stream())
 
 
 def reduce_scatter_bf16_accum(full_grad_ptrs, dst_shard, src_offset, n, scale, rank, world, max_ctas=0):

@@ -159,6 +159,18 @@ class ShardedGPT:
         self.grad_pool = [SymmetricBuffer(blk, torch.float32, dev) for _ in range(2)]
         self.comm_stream = torch.cuda.Stream(device=dev)
         self.max_ctas = 0
+        # all-gather fused into the QKV GEMM (B200_FSDP_FUSE_AG=0 gathers those rows with the rest of the unit)
+        import os as _os
+
+        self._unit_ptr_cache: Dict[int, Any] = {}
+        h = model.config.hidden_size
+        self.qkv_len = 3 * h * h
+        self.qkv_off = (st.by_name["layers.0.attention.q_proj.weight"].offset - self.units[1].lo) if self.L > 0 else 0
+        self.fuse_ag = (_os.environ.get("B200_FSDP_FUSE_AG", "1") != "0" and self.L > 0
+                        and min(self.unit_part[1:]) >= 16384 and 3 * h >= 256)
+        self.ag_pairs = int(_os.environ.get("B200_FSDP_AG_PAIRS", "4"))
+        self._ag_flags = [torch.zeros((3 * h + 127) // 128, dtype=torch.int32, device=dev) for _ in self.gather_pool]
+        self._ag_epoch = 0
         # engine bound to hooks
         self.engine = FusedGPTEngine.__new__(FusedGPTEngine)
         self._init_engine(model, seed, LayerWeights)
@@ -236,16 +248,44 @@ class ShardedGPT:
         e.g_emb = rootv(self.root_g.local, "embed_tokens.weight")
         e.g_norm = rootv(self.root_g.local, "norm.weight")
         e.w_layers, e.g_layers = [], [None] * self.L
+        e.ag_hook = self._ag_hook
         e.weights_hook = self._weights_hook
         e.release_hook = self._release_hook
         e.grad_ready_hook = self._grad_ready_hook
 
     # ------------------------------------------------------------------------------------------ gathers
-    def _gather_unit(self, u: int, dst: torch.Tensor) -> None:
+    def _unit_ptrs(self, u: int):
+        """Pointer table (one entry per rank) of unit u's slice inside every rank's bf16 shard."""
+        tab = self._unit_ptr_cache.get(u)
+        if tab is None:
+            tab = self.shard_bf16.offset_ptrs(self.shard_off[u] * 2)
+            self._unit_ptr_cache[u] = tab
+        return tab
+
+    def _gather_unit(self, u: int, dst: torch.Tensor, skip_qkv: bool = False) -> None:
+        """All-gather of unit u.  ``skip_qkv``: leave the q|k|v rows alone -- the QKV GEMM of this block gathers
+        them itself (all-gather fused into the first consuming GEMM, ``b200_gemm2_ag_bf16``)."""
         from ..ops import kernels as K
 
-        K.all_gather_bf16(self.shard_bf16.offset_ptrs(self.shard_off[u] * 2), dst, self.unit_part[u], self.rank,
-                          self.world, self.max_ctas)
+        excl = (self.qkv_off, self.qkv_off + self.qkv_len) if skip_qkv else (0, 0)
+        K.all_gather_bf16(self._unit_ptrs(u), dst, self.unit_part[u], self.rank, self.world, self.max_ctas,
+                          exclude=excl)
+
+    def _fuse_qkv_now(self) -> bool:
+        """Will the QKV GEMM run on the weights gathered in the current phase?  Forward: always.  Backward:
+        only when the block forward is recomputed (activation checkpointing)."""
+        return self.fuse_ag and (self._phase == "forward" or self.engine.checkpointing)
+
+    def _ag_hook(self, l: int):
+        """Fused all-gather arguments for block l's QKV GEMM, or None if its rows are already in place."""
+        ent = self._gathered.get(l)
+        if ent is None or not ent[2]:
+            return None
+        slot = ent[0]
+        self._gathered[l] = (slot, ent[1], False)
+        self._ag_epoch += 1
+        return (self._unit_ptrs(1 + l), self.unit_part[1 + l], self.qkv_off, self._ag_flags[slot], self._ag_epoch,
+                self.rank, self.world, self.ag_pairs)
 
     def _acquire_slot(self, l: int) -> int:
         for i, owner in enumerate(self._slot_owner):
@@ -263,16 +303,17 @@ class ShardedGPT:
         cs = self.comm_stream
         if self._slot_free_evt[slot] is not None:
             cs.wait_event(self._slot_free_evt[slot])
+        fused = self._fuse_qkv_now()
         with torch.cuda.stream(cs):
-            self._gather_unit(1 + l, self.gather_pool[slot])
+            self._gather_unit(1 + l, self.gather_pool[slot], skip_qkv=fused)
             ev = torch.cuda.Event()
             ev.record(cs)
-        self._gathered[l] = (slot, ev)
+        self._gathered[l] = (slot, ev, fused)      # fused: the q|k|v rows are still missing
 
     def _weights_hook(self, l: int):
         if l not in self._gathered:
             self._prefetch(l)
-        slot, ev = self._gathered[l]
+        slot, ev, _ = self._gathered[l]
         torch.cuda.current_stream().wait_event(ev)
         # prefetch the unit the walk needs next
         nxt = l + 1 if self._phase == "forward" else l - 1
@@ -280,7 +321,7 @@ class ShardedGPT:
         return self._views(self.gather_pool[slot], l, self._LayerWeights)
 
     def _free_gathered(self, l: int) -> None:
-        slot, _ = self._gathered.pop(l)
+        slot = self._gathered.pop(l)[0]
         ev = torch.cuda.Event()
         ev.record(torch.cuda.current_stream())
         self._slot_free_evt[slot] = ev

@@ -216,6 +216,9 @@ int b200_allreduce_scalars(const void* const* pad_ptrs, int rank, int world, uns
 /* dst[r*shard + i] = shard_r[i]  (reference: FSDP all_gather_into_tensor, fsdp_trainer.py:379,383) */
 int b200_all_gather_bf16(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
                          int max_ctas, void* stream);
+/* Same, leaving elements [excl_lo, excl_hi) of dst untouched: the window a fused all-gather GEMM fills itself. */
+int b200_all_gather_bf16_excl(const void* const* shard_ptrs, void* dst, long long shard_elems, int rank, int world,
+                              long long excl_lo_elems, long long excl_hi_elems, int max_ctas, void* stream);
 /* dst_shard[i] += scale * sum_r full_grad_r[src_offset + i]  (reference: FSDP reduce_scatter_tensor,
  * fsdp_trainer.py:383).  fp32 wire (exact) and bf16 wire (the reference's reduce_dtype) variants. */
 int b200_reduce_scatter_f32_accum(const void* const* full_grad_ptrs, float* dst_shard, long long src_offset,
