@@ -168,7 +168,7 @@ class ShardedGPT:
         self.qkv_off = (st.by_name["layers.0.attention.q_proj.weight"].offset - self.units[1].lo) if self.L > 0 else 0
         self.fuse_ag = (_os.environ.get("B200_FSDP_FUSE_AG", "1") != "0" and self.L > 0
                         and min(self.unit_part[1:]) >= 16384 and 3 * h >= 256)
-        self.ag_pairs = int(_os.environ.get("B200_FSDP_AG_PAIRS", "4"))
+        self.ag_pairs = int(_os.environ.get("B200_FSDP_AG_PAIRS", "2"))
         self._ag_flags = [torch.zeros((3 * h + 127) // 128, dtype=torch.int32, device=dev) for _ in self.gather_pool]
         self._ag_epoch = 0
         # engine bound to hooks
