@@ -19,10 +19,11 @@ lse = torch.zeros(B, H, S, device="cuda")
 dqkv = torch.zeros(B * S, 3 * h, device="cuda", dtype=torch.bfloat16)
 delta = torch.zeros(B, H, S, device="cuda")
 dq_acc = torch.empty(B * S, h, device="cuda")
-fwd = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9)
+fwd = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=1)
+fwd2 = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=2)
 bwd = lambda: k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 9)
 fwd(); bwd(); torch.cuda.synchronize()
 if os.environ.get("ATTN_TIME", "1") == "1":
     fl = 4.0 * B * H * S * S * 64 / 2
-    tf, tb = timeit(fwd), timeit(bwd)
-    print(f"p={p}: fwd {tf*1e3:.1f} us ({fl/tf/1e9:.0f} TFLOP/s causal)  bwd {tb*1e3:.1f} us ({2.5*fl/tb/1e9:.0f} TFLOP/s)")
+    tf, tb, tf2 = timeit(fwd), timeit(bwd), timeit(fwd2)
+    print(f"p={p}: fwd {tf*1e3:.1f} us ({fl/tf/1e9:.0f} TFLOP/s causal)  fwd2 {tf2*1e3:.1f} us ({fl/tf2/1e9:.0f})  bwd {tb*1e3:.1f} us ({2.5*fl/tb/1e9:.0f} TFLOP/s)")

@@ -57,6 +57,12 @@ struct AttnParams {
 __device__ __forceinline__ uint32_t swz(uint32_t tile_base, int row, int cc) {
   return tile_base + row * 128 + ((cc ^ (row & 7)) << 4);
 }
+// single MUFU.EX2 (exp2f() adds a denormal-range compare and two predicated multiplies per element)
+__device__ __forceinline__ float ex2_ftz(float x) {
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -190,7 +196,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     const int qrow = qi * kBlk + r;               // position in the sequence
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
-    const uint32_t thresh = dropout_threshold16(p.p_drop);
+    const uint32_t thresh_hi = dropout_threshold16(p.p_drop) << 16;
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
     const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
@@ -223,37 +229,41 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       __syncwarp();
       tmem_ld_32x32b_x32(tS[st] + lane_off + qt * 32, v);
       tmem_ld_wait();
-      float s[32];
+      // The causal mask only touches the diagonal tile: a warp-uniform branch keeps the compare +
+      // select out of every other tile.  Scores stay raw (unscaled) -- the 1/sqrt(d) * log2(e) factor
+      // is folded into the exponent's FFMA below, and max commutes with a positive scale.
+      if (diag) {
 #pragma unroll
-      for (int e = 0; e < 32; ++e) {
-        s[e] = __uint_as_float(v[e]) * kScale2;
-        if (diag && (qt * 32 + e) > r) s[e] = -INFINITY;
+        for (int e = 0; e < 32; ++e)
+          if ((qt * 32 + e) > r) v[e] = 0xFF800000u;   // -inf
       }
       float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains instead of one serial max
 #pragma unroll
-      for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], s[e]);
+      for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], __uint_as_float(v[e]));
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       xchg[(st * 4 + qt) * 128 + r] = mx;
       softmax_bar_sync();
 #pragma unroll
       for (int t = 0; t < 4; ++t) mx = fmaxf(mx, xchg[(st * 4 + t) * 128 + r]);
       mx = fmaxf(mx, m);
-      const float m_use = (mx == -INFINITY) ? 0.f : mx;
-      const float alpha = exp2f(m - m_use);
+      const float m_use = (mx == -INFINITY) ? 0.f : mx;   // m, m_use: running max of the RAW scores
+      const float alpha = ex2_ftz((m - m_use) * kScale2);
+      const float neg_msc = -m_use * kScale2;
       // probabilities -> smem (bf16, dropout applied, unnormalised)
       const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + (qt >> 1) * kTile;
       float l4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
-        uint32_t keep = 0xFF;
-        if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3), thresh);
         float pv[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const float pe = exp2f(s[g * 8 + e] - m_use);   // masked entries are exp2(-inf) = 0
-          l4[e & 3] += pe;
-          pv[e] = ((keep >> e) & 1) ? pe : 0.f;
+          // one FFMA + one MUFU per element; masked entries are ex2(-inf) = 0
+          pv[e] = ex2_ftz(fmaf(__uint_as_float(v[g * 8 + e]), kScale2, neg_msc));
+          l4[e & 3] += pv[e];
         }
+        if (drop)
+          dropout_zero8(dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3)),
+                        thresh_hi, pv);
         st_shared_v4(swz(sub, r, (qt & 1) * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
                      pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
       }
@@ -290,7 +300,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         *reinterpret_cast<uint4*>(dst + g * 8) =
             make_uint4(pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv), pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv),
                        pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv), pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv));
-      if (qt == 0) p.lse[size_t(b * p.H + hd) * p.S + qrow] = m + log2f(l);
+      if (qt == 0) p.lse[size_t(b * p.H + hd) * p.S + qrow] = m * kScale2 + log2f(l);
     }
   }
 
@@ -345,11 +355,12 @@ struct BwdSmem {
   static constexpr int kV = kK + kTile;
   static constexpr int kQ = kV + kTile;            // 2 stages
   static constexpr int kdO = kQ + 2 * kTile;       // 2 stages
-  static constexpr int kP = kdO + 2 * kTile;       // 32 KB
-  static constexpr int kdS = kP + kPTile;          // 32 KB
-  static constexpr int kBars = kdS + kPTile;
+  static constexpr int kP = kdO + 2 * kTile;       // 2 buffers x 32 KB
+  static constexpr int kdS = kP + 2 * kPTile;      // 2 buffers x 32 KB
+  static constexpr int kBars = kdS + 2 * kPTile;
   static constexpr int kTotal = kBars + 256 + 1024;
 };
+static_assert(BwdSmem::kTotal <= 227 * 1024, "backward smem exceeds the 227 KB per-CTA limit");
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
@@ -362,11 +373,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   uint64_t* qdo_empty = bars + 3;      // 2
   uint64_t* sdp_full = bars + 5;       // 1
   uint64_t* s_free = bars + 6;         // 1 (count 4)
-  uint64_t* pds_ready = bars + 7;      // 1 (count 4)
-  uint64_t* dq_full = bars + 8;        // 1
-  uint64_t* dq_free = bars + 9;        // 1 (count 4)
-  uint64_t* acc_full = bars + 10;      // 1
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 11);
+  uint64_t* pds_ready = bars + 7;      // 2 (count = softmax warps)
+  uint64_t* dq_full = bars + 9;        // 2
+  uint64_t* dq_free = bars + 11;       // 2 (count = softmax warps)
+  uint64_t* acc_full = bars + 13;      // 1
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + kBlk - 1) / kBlk;
@@ -386,9 +397,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
     mbar_init(sdp_full, 1);
     mbar_init(s_free, kSoftmaxWarps);
-    mbar_init(pds_ready, kSoftmaxWarps);
-    mbar_init(dq_full, 1);
-    mbar_init(dq_free, kSoftmaxWarps);
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&pds_ready[i], kSoftmaxWarps);
+      mbar_init(&dq_full[i], 1);
+      mbar_init(&dq_free[i], kSoftmaxWarps);
+    }
     mbar_init(acc_full, 1);
     fence_barrier_init();
   }
@@ -421,12 +434,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const uint32_t k_addr = smem_u32(smem + BwdSmem::kK), v_addr = smem_u32(smem + BwdSmem::kV);
       const uint32_t p_addr = smem_u32(smem + BwdSmem::kP), ds_addr = smem_u32(smem + BwdSmem::kdS);
       mbar_wait(kv_full, 0);
-      for (int it = 0; it < niter; ++it) {
+      // S = Q K^T and dP = dO V^T of q block `it` (one TMEM buffer each; the element-wise warps free
+      // it as soon as both are in registers, so block it+1's pair runs under block it's softmax).
+      auto issue_sdp = [&](int it) {
         const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
         const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
         const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
-        mbar_wait(&qdo_full[st], ph);
+        mbar_wait(&qdo_full[st], (it >> 1) & 1);
         mbar_wait(s_free, (it & 1) ^ 1);
         tc_fence_after();
 #pragma unroll
@@ -438,23 +452,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           umma_bf16_ss(tdP, make_smem_desc_sw128(do_addr + t * 32, 16, 1024), make_smem_desc_sw128(v_addr + t * 32, 16, 1024),
                        idesc_s, t > 0);
         tc_commit(sdp_full);
-        mbar_wait(pds_ready, it & 1);
-        mbar_wait(dq_free, (it & 1) ^ 1);
+      };
+      issue_sdp(0);
+      for (int it = 0; it < niter; ++it) {
+        const int st = it & 1;                 // Q/dO stage, P/dS buffer and dQ buffer of this block
+        const uint32_t use = (it >> 1) & 1;
+        const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
+        const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
+        const uint32_t pb = p_addr + st * kPTile, dsb = ds_addr + st * kPTile;
+        if (it + 1 < niter) issue_sdp(it + 1);
+        mbar_wait(&pds_ready[st], use);
+        mbar_wait(&dq_free[st], use ^ 1);
         tc_fence_after();
 #pragma unroll
         for (int t = 0; t < 8; ++t)  // dV += P~^T dO   (K = 128 q rows, 16 per step)
-          umma_bf16_ss(tdV, make_smem_desc_sw128(p_addr + t * 2048, kTile, 1024),
+          umma_bf16_ss(tdV, make_smem_desc_sw128(pb + t * 2048, kTile, 1024),
                        make_smem_desc_sw128(do_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
 #pragma unroll
         for (int t = 0; t < 8; ++t)  // dK += dS^T Q
-          umma_bf16_ss(tdK, make_smem_desc_sw128(ds_addr + t * 2048, kTile, 1024),
+          umma_bf16_ss(tdK, make_smem_desc_sw128(dsb + t * 2048, kTile, 1024),
                        make_smem_desc_sw128(q_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
 #pragma unroll
         for (int t = 0; t < 8; ++t)  // dQ_i = dS K     (K = 128 kv, 16 per step)
-          umma_bf16_ss(tdQ, make_smem_desc_sw128(ds_addr + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
+          umma_bf16_ss(tdQ + st * 64, make_smem_desc_sw128(dsb + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
                        make_smem_desc_sw128(k_addr + t * 2048, kTile, 1024), idesc_dq, t > 0);
         tc_commit(&qdo_empty[st]);
-        tc_commit(dq_full);
+        tc_commit(&dq_full[st]);
       }
       tc_commit(acc_full);
     }
@@ -464,21 +487,22 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const int r = qd * 32 + lane;
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
-    const uint32_t thresh = dropout_threshold16(p.p_drop);
-    const float inv_keep = drop ? 1.f / (1.f - p.p_drop) : 1.f;
+    const uint32_t thresh_hi = dropout_threshold16(p.p_drop) << 16;
+    const float log2_inv_keep = drop ? -log2f(1.f - p.p_drop) : 0.f;
+    const float keep_scale = (drop ? 1.f - p.p_drop : 1.f) * kScale;
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
-    const uint32_t p_sub = smem_u32(smem + BwdSmem::kP) + (qt >> 1) * kTile;
-    const uint32_t ds_sub = smem_u32(smem + BwdSmem::kdS) + (qt >> 1) * kTile;
+    const uint32_t p_sub0 = smem_u32(smem + BwdSmem::kP) + (qt >> 1) * kTile;
+    const uint32_t ds_sub0 = smem_u32(smem + BwdSmem::kdS) + (qt >> 1) * kTile;
 
     auto drain_dq = [&](int it) {
       const int qrow = (j + it) * kBlk + r;
-      mbar_wait(dq_full, it & 1);
+      mbar_wait(&dq_full[it & 1], (it >> 1) & 1);
       tc_fence_after();
       float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + qt * 16;
       uint32_t v[16];
       __syncwarp();
-      tmem_ld_32x32b_x16(tdQ + lane_off + qt * 16, v);
+      tmem_ld_32x32b_x16(tdQ + (it & 1) * 64 + lane_off + qt * 16, v);
       tmem_ld_wait();
       if (qrow < p.S) {
 #pragma unroll
@@ -490,17 +514,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(dq_free);
+      if (lane == 0) mbar_arrive(&dq_free[it & 1]);
     };
 
+    // Block `it` writes P~/dS buffer it&1; the MMAs of block it-2 that read it have completed because
+    // dQ(it-2) was drained (dq_full covers every earlier MMA) during block it-1.  The drain of dQ(it-1)
+    // comes AFTER this block's element-wise work so its MMAs run underneath that work.
     for (int it = 0; it < niter; ++it) {
-      if (it > 0) drain_dq(it - 1);
       const int i = j + it;
       const int qrow = i * kBlk + r;
       const bool diag = (i == j);
       const bool row_ok = qrow < p.S;
       const size_t stat = size_t(b * p.H + hd) * p.S + (row_ok ? qrow : 0);
-      const float lse2 = row_ok ? p.lse[stat] : INFINITY;
+      const float neg_lse = row_ok ? log2_inv_keep - p.lse[stat] : -INFINITY;
       const float dl = row_ok ? p.delta[stat] : 0.f;
       const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
       mbar_wait(sdp_full, it & 1);
@@ -510,20 +536,33 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tmem_ld_32x32b_x32(tS + lane_off + qt * 32, sv);
       tmem_ld_32x32b_x32(tdP + lane_off + qt * 32, dv);
       tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);   // S / dP are in registers: the next block's pair may overwrite them
+      const uint32_t p_sub = p_sub0 + (it & 1) * kPTile, ds_sub = ds_sub0 + (it & 1) * kPTile;
+      if (diag) {   // causal mask: only the diagonal tile pays for it (warp-uniform branch)
+#pragma unroll
+        for (int e = 0; e < 32; ++e)
+          if ((qt * 32 + e) > r) sv[e] = 0xFF800000u;   // -inf -> probability 0 -> dS 0
+      }
+      // With q = 1/(1-p):  P~ = keep ? q P : 0  and  dS = P (dP~ - delta) / sqrt(d),  dP~ = keep ? q dP : 0.
+      // Folding q into the exponent gives qP from one FFMA + MUFU, and
+      //   dS = qP * (keep ? dP/sqrt(d) - c : -c),  c = delta (1-p) / sqrt(d)
+      // so an element costs FFMA, MUFU, compare, 2 selects, FFMA, FMUL and its share of two packs.
+      const float neg_c = -dl * keep_scale;
 #pragma unroll
       for (int g = 0; g < 4; ++g) {
-        uint32_t keep = 0xFF;
-        if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3), thresh);
+        uint4 rb = make_uint4(0u, 0u, 0u, 0u);   // thresh_hi is 0 without dropout: every lane kept
+        if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3));
+        const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
         float pd[8], ds[8];
 #pragma unroll
         for (int e = 0; e < 8; ++e) {
-          const int col = qt * 32 + g * 8 + e;
-          float pe = exp2f(__uint_as_float(sv[g * 8 + e]) * kScale2 - lse2);
-          if (diag && col > r) pe = 0.f;
-          const bool k1 = (keep >> e) & 1;
-          const float dpe = k1 ? __uint_as_float(dv[g * 8 + e]) * inv_keep : 0.f;
-          ds[e] = pe * (dpe - dl) * kScale;
-          pd[e] = k1 ? pe * inv_keep : 0.f;
+          const float qp = ex2_ftz(fmaf(__uint_as_float(sv[g * 8 + e]), kScale2, neg_lse));
+          const bool k1 = ((e & 1) ? w[e >> 1] : (w[e >> 1] << 16)) >= thresh_hi;
+          const float t = fmaf(__uint_as_float(dv[g * 8 + e]), kScale, neg_c);
+          ds[e] = qp * (k1 ? t : neg_c);
+          pd[e] = k1 ? qp : 0.f;
         }
         const int cc = (qt & 1) * 4 + g;
         st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
@@ -534,10 +573,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       tc_fence_before();
       fence_proxy_async_smem();
       __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(pds_ready);
-        mbar_arrive(s_free);
-      }
+      if (lane == 0) mbar_arrive(&pds_ready[it & 1]);
+      if (it > 0) drain_dq(it - 1);
     }
     drain_dq(niter - 1);
 

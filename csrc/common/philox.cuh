@@ -51,4 +51,17 @@ __device__ __forceinline__ uint32_t dropout_keep8(unsigned long long seed, unsig
   return keep;
 }
 
+// Select form of the same mask for the attention kernels: zeroes the dropped ones among eight values
+// without materialising the bit mask.  thresh_hi = threshold << 16; a 16-bit lane is kept when
+// lane >= threshold, which for the high lane is  w >= thresh_hi  and for the low lane
+// (w << 16) >= thresh_hi  -- one compare (plus a shift for the low lane) and one select per element.
+__device__ __forceinline__ void dropout_zero8(const uint4 r, uint32_t thresh_hi, float (&v)[8]) {
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    v[2 * i] = ((w[i] << 16) >= thresh_hi) ? v[2 * i] : 0.f;
+    v[2 * i + 1] = (w[i] >= thresh_hi) ? v[2 * i + 1] : 0.f;
+  }
+}
+
 }  // namespace b200

@@ -18,7 +18,8 @@ def _attn_mask(B, H, S, p, rng, stream):
 
 @pytest.mark.parametrize("B,S,H,p", [(2, 128, 2, 0.0), (1, 512, 3, 0.0), (2, 384, 2, 0.1), (1, 200, 2, 0.1),
                                      (2, 1024, 4, 0.1)])
-def test_attention_fwd_bwd(B, S, H, p):
+@pytest.mark.parametrize("impl", [1, 2])
+def test_attention_fwd_bwd(B, S, H, p, impl):
     from distributed_llm_trainer_b200.ops import kernels as k
     from distributed_llm_trainer_b200.ops import reference as R
 
@@ -28,7 +29,7 @@ def test_attention_fwd_bwd(B, S, H, p):
     rng = torch.tensor([42, 3], dtype=torch.int64, device="cuda")
     out = torch.zeros(B * S, h, device="cuda", dtype=torch.bfloat16)
     lse = torch.zeros(B, H, S, device="cuda")
-    k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9)
+    k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=impl)
     torch.cuda.synchronize()
 
     def split(t):
