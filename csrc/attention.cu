@@ -81,7 +81,10 @@ struct FwdSmem {
 constexpr int kSoftmaxWarps = 16;   // four per scheduler: each thread owns one row x 32 score columns
 constexpr int kAttnThreads = 64 + kSoftmaxWarps * 32;
 
-__device__ __forceinline__ void softmax_bar_sync() { asm volatile("bar.sync 1, 512;" ::: "memory"); }
+// The four threads that share a score row sit in the four warps with the same lane quarter `qd`
+// (one per 32-column quarter), so the row-max exchange only needs those 128 threads: one named
+// barrier per quarter instead of one over all 512 softmax threads.
+__device__ __forceinline__ void softmax_bar_sync(int qd) { asm volatile("bar.sync %0, 128;" ::"r"(qd + 1) : "memory"); }
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
@@ -242,7 +245,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], __uint_as_float(v[e]));
       float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
       xchg[(st * 4 + qt) * 128 + r] = mx;
-      softmax_bar_sync();
+      softmax_bar_sync(qd);
 #pragma unroll
       for (int t = 0; t < 4; ++t) mx = fmaxf(mx, xchg[(st * 4 + t) * 128 + r]);
       mx = fmaxf(mx, m);
@@ -288,9 +291,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     }
     fold_o((nkv - 1) & 1, ((nkv - 1) >> 1) & 1, alpha_prev);
     // total row sum = the four column-quarters' partial sums (same running max on all four threads)
-    softmax_bar_sync();
+    softmax_bar_sync(qd);
     xchg[qt * 128 + r] = l;
-    softmax_bar_sync();
+    softmax_bar_sync(qd);
     l = (xchg[r] + xchg[128 + r]) + (xchg[256 + r] + xchg[384 + r]);
     if (qrow < p.S) {
       const float inv = (drop ? 1.f / (1.f - p.p_drop) : 1.f) / l;
@@ -520,14 +523,19 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     // Block `it` writes P~/dS buffer it&1; the MMAs of block it-2 that read it have completed because
     // dQ(it-2) was drained (dq_full covers every earlier MMA) during block it-1.  The drain of dQ(it-1)
     // comes AFTER this block's element-wise work so its MMAs run underneath that work.
+    // per-row statistics are fetched one block ahead so their global-load latency hides under the math
+    const float* lse_bh = p.lse + size_t(b * p.H + hd) * p.S;
+    const float* delta_bh = p.delta + size_t(b * p.H + hd) * p.S;
+    float lse_nx = 0.f, dl_nx = 0.f;
+    if (j * kBlk + r < p.S) { lse_nx = lse_bh[j * kBlk + r]; dl_nx = delta_bh[j * kBlk + r]; }
     for (int it = 0; it < niter; ++it) {
       const int i = j + it;
       const int qrow = i * kBlk + r;
       const bool diag = (i == j);
       const bool row_ok = qrow < p.S;
-      const size_t stat = size_t(b * p.H + hd) * p.S + (row_ok ? qrow : 0);
-      const float neg_lse = row_ok ? log2_inv_keep - p.lse[stat] : -INFINITY;
-      const float dl = row_ok ? p.delta[stat] : 0.f;
+      const float neg_lse = row_ok ? log2_inv_keep - lse_nx : -INFINITY;
+      const float dl = row_ok ? dl_nx : 0.f;
+      if (it + 1 < niter && qrow + kBlk < p.S) { lse_nx = lse_bh[qrow + kBlk]; dl_nx = delta_bh[qrow + kBlk]; }
       const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
       mbar_wait(sdp_full, it & 1);
       tc_fence_after();
