@@ -87,7 +87,11 @@ __global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const __nv_bfloa
 // Persistent warps stride over rows and keep their dw partials in registers (columns owned by a lane
 // are fixed), then one smem reduction + one red.add per column per CTA.
 constexpr int kNormMaxVec = 8;  // 8 x (8 columns) x 32 lanes = 2048 columns max
-__global__ void __launch_bounds__(256)
+// NV = ceil(hidden / 256): vectors of 8 columns per lane.  A row's dy / x / dx are all requested up
+// front (NV x 80 bytes per lane in flight) and stay in registers for both the dot product and the
+// update, so the row is read exactly once; w is loaded once per warp.
+template <int NV>
+__global__ void __launch_bounds__(256, NV <= 3 ? 2 : 1)
 rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x,
                    const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd, float* __restrict__ dx,
                    float* __restrict__ dw, int rows, int hidden) {
@@ -96,61 +100,74 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict
   __syncthreads();
   const int warps = blockDim.x >> 5, wid = threadIdx.x >> 5, lane = lane_id();
   const int nvec = hidden / 8;
-  float acc[kNormMaxVec][8];
+  float acc[NV][8];
+  uint4 wq[NV];   // this lane's weight columns, kept packed (unpacking is a shift / mask)
 #pragma unroll
-  for (int k = 0; k < kNormMaxVec; ++k)
+  for (int k = 0; k < NV; ++k) {
+    const int i = lane + 32 * k;
+    wq[k] = i < nvec ? reinterpret_cast<const uint4*>(w)[i] : make_uint4(0, 0, 0, 0);
 #pragma unroll
     for (int e = 0; e < 8; ++e) acc[k][e] = 0.f;
-  const uint4* wr = reinterpret_cast<const uint4*>(w);
+  }
+  const float inv_h = 1.f / float(hidden);
   for (int row = blockIdx.x * warps + wid; row < rows; row += gridDim.x * warps) {
     const uint4* dyr = reinterpret_cast<const uint4*>(dy + size_t(row) * hidden);
     const float4* xr = reinterpret_cast<const float4*>(x + size_t(row) * hidden);
     float4* dxr = reinterpret_cast<float4*>(dx + size_t(row) * hidden);
+    uint4 dq[NV];
+    float4 xa[NV], xb[NV], oa[NV], ob[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nvec) {
+        dq[k] = dyr[i];
+        xa[k] = xr[2 * i];
+        xb[k] = xr[2 * i + 1];
+        oa[k] = dxr[2 * i];
+        ob[k] = dxr[2 * i + 1];
+      } else {
+        dq[k] = make_uint4(0, 0, 0, 0);
+        xa[k] = xb[k] = oa[k] = ob[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
     const float r = rstd[row];
     float dot = 0.f;
 #pragma unroll
-    for (int k = 0; k < kNormMaxVec; ++k) {
-      const int i = lane + 32 * k;
-      if (i < nvec) {
-        const uint4 dq = dyr[i], wq = wr[i];
-        const float4 a = xr[2 * i], b = xr[2 * i + 1];
-        const float xs[8] = {a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w};
-        const uint32_t dqw[4] = {dq.x, dq.y, dq.z, dq.w}, wqw[4] = {wq.x, wq.y, wq.z, wq.w};
+    for (int k = 0; k < NV; ++k) {
+      const float xs[8] = {xa[k].x, xa[k].y, xa[k].z, xa[k].w, xb[k].x, xb[k].y, xb[k].z, xb[k].w};
+      const uint32_t dqw[4] = {dq[k].x, dq[k].y, dq[k].z, dq[k].w};
+      const uint32_t wqw[4] = {wq[k].x, wq[k].y, wq[k].z, wq[k].w};
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const float2 d2 = unpack_bf16x2(dqw[e]), w2 = unpack_bf16x2(wqw[e]);
-          dot += d2.x * w2.x * xs[2 * e] + d2.y * w2.y * xs[2 * e + 1];
-          acc[k][2 * e] += d2.x * xs[2 * e] * r;
-          acc[k][2 * e + 1] += d2.y * xs[2 * e + 1] * r;
-        }
+      for (int e = 0; e < 4; ++e) {
+        const float2 d2 = unpack_bf16x2(dqw[e]), w2 = unpack_bf16x2(wqw[e]);
+        dot += d2.x * w2.x * xs[2 * e] + d2.y * w2.y * xs[2 * e + 1];
+        acc[k][2 * e] += d2.x * xs[2 * e] * r;
+        acc[k][2 * e + 1] += d2.y * xs[2 * e + 1] * r;
       }
     }
     dot = warp_sum(dot);
-    const float coef = dot * r * r * r / float(hidden);
+    const float coef = dot * r * r * r * inv_h;
 #pragma unroll
-    for (int k = 0; k < kNormMaxVec; ++k) {
+    for (int k = 0; k < NV; ++k) {
       const int i = lane + 32 * k;
       if (i < nvec) {
-        const uint4 dq = dyr[i], wq = wr[i];
-        const float4 a = xr[2 * i], b = xr[2 * i + 1];
-        float4 o0 = dxr[2 * i], o1 = dxr[2 * i + 1];
-        const float2 d0 = unpack_bf16x2(dq.x), d1 = unpack_bf16x2(dq.y), d2 = unpack_bf16x2(dq.z), d3 = unpack_bf16x2(dq.w);
-        const float2 w0 = unpack_bf16x2(wq.x), w1 = unpack_bf16x2(wq.y), w2 = unpack_bf16x2(wq.z), w3 = unpack_bf16x2(wq.w);
-        o0.x += r * d0.x * w0.x - a.x * coef;
-        o0.y += r * d0.y * w0.y - a.y * coef;
-        o0.z += r * d1.x * w1.x - a.z * coef;
-        o0.w += r * d1.y * w1.y - a.w * coef;
-        o1.x += r * d2.x * w2.x - b.x * coef;
-        o1.y += r * d2.y * w2.y - b.y * coef;
-        o1.z += r * d3.x * w3.x - b.z * coef;
-        o1.w += r * d3.y * w3.y - b.w * coef;
-        dxr[2 * i] = o0;
-        dxr[2 * i + 1] = o1;
+        const float2 d0 = unpack_bf16x2(dq[k].x), d1 = unpack_bf16x2(dq[k].y), d2 = unpack_bf16x2(dq[k].z), d3 = unpack_bf16x2(dq[k].w);
+        const float2 w0 = unpack_bf16x2(wq[k].x), w1 = unpack_bf16x2(wq[k].y), w2 = unpack_bf16x2(wq[k].z), w3 = unpack_bf16x2(wq[k].w);
+        oa[k].x += r * d0.x * w0.x - xa[k].x * coef;
+        oa[k].y += r * d0.y * w0.y - xa[k].y * coef;
+        oa[k].z += r * d1.x * w1.x - xa[k].z * coef;
+        oa[k].w += r * d1.y * w1.y - xa[k].w * coef;
+        ob[k].x += r * d2.x * w2.x - xb[k].x * coef;
+        ob[k].y += r * d2.y * w2.y - xb[k].y * coef;
+        ob[k].z += r * d3.x * w3.x - xb[k].z * coef;
+        ob[k].w += r * d3.y * w3.y - xb[k].w * coef;
+        dxr[2 * i] = oa[k];
+        dxr[2 * i + 1] = ob[k];
       }
     }
   }
 #pragma unroll
-  for (int k = 0; k < kNormMaxVec; ++k) {
+  for (int k = 0; k < NV; ++k) {
     const int i = lane + 32 * k;
     if (i < nvec) {
 #pragma unroll
@@ -337,8 +354,18 @@ int b200_rmsnorm_bwd(const void* dy, const float* x, const void* w, const float*
   int grid = sm_count() * 2;
   const int max_grid = (rows + 7) / 8;
   if (grid > max_grid) grid = max_grid;
-  rmsnorm_bwd_kernel<<<grid, 256, hidden * sizeof(float), STREAM(stream)>>>(
-      (const __nv_bfloat16*)dy, x, (const __nv_bfloat16*)w, rstd, dx, dw, rows, hidden);
+  const int nv = (hidden / 8 + 31) / 32;
+#define B200_NORM_BWD(NV)                                                                         \
+  case NV:                                                                                        \
+    rmsnorm_bwd_kernel<NV><<<grid, 256, hidden * sizeof(float), STREAM(stream)>>>(                \
+        (const __nv_bfloat16*)dy, x, (const __nv_bfloat16*)w, rstd, dx, dw, rows, hidden);        \
+    break;
+  switch (nv) {
+    B200_NORM_BWD(1) B200_NORM_BWD(2) B200_NORM_BWD(3) B200_NORM_BWD(4)
+    B200_NORM_BWD(5) B200_NORM_BWD(6) B200_NORM_BWD(7) B200_NORM_BWD(8)
+    default: B200_REQUIRE(false, "rmsnorm_bwd: hidden %d too large", hidden);
+  }
+#undef B200_NORM_BWD
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -15,6 +15,12 @@ namespace b200 {
 // Reference: F.cross_entropy(shift_logits, shift_labels) gpt.py:451-453 and its autograd backward.
 constexpr int kCeThreads = 512;
 
+__device__ __forceinline__ float ex2_approx_ftz(float x) {   // a single MUFU.EX2
+  float y;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 __device__ __forceinline__ float block_reduce(float v, float* scratch, bool is_max) {
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
 #pragma unroll
@@ -52,55 +58,75 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict_
     for (int i = threadIdx.x; i < nvec; i += blockDim.x) grow[i] = make_uint4(0, 0, 0, 0);
     return;
   }
-  float mx = -INFINITY;
-  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
-    const uint4 q = grow[i];
-    srow[i] = q;
-    const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+  // Pass 1: global -> smem (four independent 16-byte loads in flight per thread) + row max.  Padding
+  // columns [vocab, ld) are replaced by -inf while staging, so the later passes carry no bounds checks:
+  // they contribute exp2(-inf) = 0 to the sum and get a zero gradient.
+  float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+  for (int base = threadIdx.x; base < nvec; base += 4 * kCeThreads) {
+    uint4 q[4];
 #pragma unroll
-    for (int e = 0; e < 4; ++e) {
-      const float2 f = unpack_bf16x2(w[e]);
-      const int c = i * 8 + 2 * e;
-      if (c < vocab) mx = fmaxf(mx, f.x);
-      if (c + 1 < vocab) mx = fmaxf(mx, f.y);
+    for (int u = 0; u < 4; ++u) {
+      const int i = base + u * kCeThreads;
+      q[u] = i < nvec ? grow[i] : make_uint4(0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u, 0xFF80FF80u);
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int i = base + u * kCeThreads;
+      uint32_t w[4] = {q[u].x, q[u].y, q[u].z, q[u].w};
+      if (i * 8 + 8 > vocab) {
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const int c = i * 8 + 2 * e;
+          if (c >= vocab) w[e] = (w[e] & 0xFFFF0000u) | 0xFF80u;
+          if (c + 1 >= vocab) w[e] = (w[e] & 0x0000FFFFu) | 0xFF800000u;
+        }
+      }
+      if (i < nvec) srow[i] = make_uint4(w[0], w[1], w[2], w[3]);
+#pragma unroll
+      for (int e = 0; e < 4; ++e) {
+        const float2 f = unpack_bf16x2(w[e]);
+        mx4[e] = fmaxf(mx4[e], fmaxf(f.x, f.y));
+      }
     }
   }
-  mx = block_reduce(mx, scratch, true);
+  float mx = block_reduce(fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])), scratch, true);
   constexpr float kLog2e = 1.4426950408889634f;
-  const float mxs = mx * kLog2e;
-  float sum = 0.f;
-  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+  const float neg_mxs = -mx * kLog2e;
+  // Pass 2: sum of exp (one FFMA + one MUFU per element).
+  float s4[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
     const uint4 q = srow[i];
     const uint32_t w[4] = {q.x, q.y, q.z, q.w};
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const float2 f = unpack_bf16x2(w[e]);
-      const int c = i * 8 + 2 * e;
-      if (c < vocab) sum += exp2f(f.x * kLog2e - mxs);
-      if (c + 1 < vocab) sum += exp2f(f.y * kLog2e - mxs);
+      s4[e] += ex2_approx_ftz(fmaf(f.x, kLog2e, neg_mxs)) + ex2_approx_ftz(fmaf(f.y, kLog2e, neg_mxs));
     }
   }
-  sum = block_reduce(sum, scratch, false);
+  const float sum = block_reduce((s4[0] + s4[1]) + (s4[2] + s4[3]), scratch, false);
   const float inv = grad_scale / sum;
   if (threadIdx.x == 0) {
     const float xl = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(srow)[label]);
     atomicAdd(loss_sum, (logf(sum) + mx - xl) * loss_scale);
   }
-  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+  // Pass 3: gradient (softmax - onehot) * grad_scale, written over the logits.
+  const int lab_vec = int(label >> 3), lab_e = int(label & 7);
+  for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
     const uint4 q = srow[i];
     const uint32_t w[4] = {q.x, q.y, q.z, q.w};
-    uint32_t o[4];
+    float g[8];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const float2 f = unpack_bf16x2(w[e]);
-      const int c = i * 8 + 2 * e;
-      float g0 = c < vocab ? exp2f(f.x * kLog2e - mxs) * inv : 0.f;
-      float g1 = c + 1 < vocab ? exp2f(f.y * kLog2e - mxs) * inv : 0.f;
-      if (c == label) g0 -= grad_scale;
-      if (c + 1 == label) g1 -= grad_scale;
-      o[e] = pack_bf16x2(g0, g1);
+      g[2 * e] = ex2_approx_ftz(fmaf(f.x, kLog2e, neg_mxs)) * inv;
+      g[2 * e + 1] = ex2_approx_ftz(fmaf(f.y, kLog2e, neg_mxs)) * inv;
     }
-    grow[i] = make_uint4(o[0], o[1], o[2], o[3]);
+    if (i == lab_vec) {
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        if (e == lab_e) g[e] -= grad_scale;
+    }
+    grow[i] = make_uint4(pack_bf16x2(g[0], g[1]), pack_bf16x2(g[2], g[3]), pack_bf16x2(g[4], g[5]), pack_bf16x2(g[6], g[7]));
   }
 }
 
