@@ -47,11 +47,15 @@ struct Cfg {
   static constexpr int kBStage = BNH * BK * 2;
   static constexpr int kStage = kAStage + kBStage;
   static constexpr int kEpiBufs = (EPI == EPI_SWIGLU_BWD) ? 6 : 4;
-  static constexpr int kStages = (EPI == EPI_SWIGLU_BWD) ? 4 : (BNP == 256 ? 5 : 6);
+  static constexpr int kStages = (EPI == EPI_SWIGLU_BWD || BNP == 384) ? 4 : (BNP == 256 ? 5 : 6);
   static constexpr int kEpiOff = kStages * kStage;
   static constexpr int kBarOff = kEpiOff + kEpiBufs * kEpiBuf;
   static constexpr int kSmemTotal = kBarOff + 256 + 1024;
-  static constexpr uint32_t kTmemCols = 2 * BNP;             // double-buffered accumulator
+  // Accumulator: double buffered, except the 384-wide tile (N = 768 problems: 64 tiles = one wave on 74
+  // pairs instead of two 65%-full waves of 256-wide tiles), which owns 384 of the 512 columns once.
+  static constexpr int kAccBufs = BNP == 384 ? 1 : 2;
+  static constexpr uint32_t kTmemCols = BNP == 384 ? 512 : 2 * BNP;
+  static_assert(BNP != 384 || EPI == EPI_BF16 || EPI == EPI_RESID_DROPOUT, "384-wide tile: plain / residual epilogues only");
   static_assert(kSmemTotal <= 232448, "shared memory budget exceeded");
 };
 
@@ -266,7 +270,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
 #pragma unroll
             for (int c = 0; c < BM / 64; ++c) tma_load_2d_cg2(sa + c * (BK * 128), &tma_a, &full_bar[stage], m0 + c * 64, k0);
           }
-          if constexpr (!B_MN) {
+          if constexpr (BNP == 384) {
+            // Two MMAs cover the tile: N = 256 (accumulator columns 0..255) then N = 128 (256..383); each
+            // takes half of its B rows from each CTA.  Staging chunks 0,1 from tile columns
+            // [128 rank, +128) and chunk 2 from [256 + 64 rank, +64) makes accumulator column j == tile
+            // column j.  A 64-row chunk is 8 KB in both operand layouts.
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+              const int nc = nt + (c < 2 ? int(cta_rank) * 128 + c * 64 : 256 + int(cta_rank) * 64);
+              if constexpr (!B_MN) tma_load_2d_cg2(sb + c * 8192, &tma_b, &full_bar[stage], k0, nc);
+              else                 tma_load_2d_cg2(sb + c * 8192, &tma_b, &full_bar[stage], nc, k0);
+            }
+          } else if constexpr (!B_MN) {
             tma_load_2d_cg2(sb, &tma_b, &full_bar[stage], k0, n0);
           } else {
 #pragma unroll
@@ -279,7 +294,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer (leader CTA only)
     if (leader && lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BNP, A_MN, B_MN);
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BNP == 384 ? 256 : BNP, A_MN, B_MN);
+      constexpr uint32_t idesc_tail = make_idesc_bf16(2 * BM, 128, A_MN, B_MN);   // 384-wide tile: columns 256..383
       int stage = 0;
       uint32_t phase = 0;
       int it = 0;
@@ -287,8 +303,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         const int ks = t / tiles_mn;
         const int kb0 = ks * p.k_per_split;
         const int kb1 = min(k_blocks_total, kb0 + p.k_per_split);
-        const int buf = it & 1;
-        const uint32_t buf_phase = (it >> 1) & 1;
+        const int buf = C::kAccBufs == 2 ? (it & 1) : 0;
+        const uint32_t buf_phase = C::kAccBufs == 2 ? ((it >> 1) & 1) : (it & 1);
         mbar_wait(&tmem_empty[buf], buf_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + buf * BNP;
@@ -304,6 +320,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             const uint64_t db = B_MN ? make_smem_desc_sw128(b_addr + j * (UMMA_K * 128), BK * 128, 1024)
                                      : make_smem_desc_sw128(b_addr + j * (UMMA_K * 2), 16, 1024);
             umma_bf16_ss_cg2(d_tmem, da, db, idesc, (kb > kb0 || j > 0) ? 1u : 0u);
+            if constexpr (BNP == 384) {
+              // third 64-row chunk of this CTA's B stage (16 KB in, either layout)
+              const uint64_t db2 = B_MN ? make_smem_desc_sw128(b_addr + 16384 + j * (UMMA_K * 128), BK * 128, 1024)
+                                        : make_smem_desc_sw128(b_addr + 16384 + j * (UMMA_K * 2), 16, 1024);
+              umma_bf16_ss_cg2(d_tmem + 256, da, db2, idesc_tail, (kb > kb0 || j > 0) ? 1u : 0u);
+            }
           }
           tc_commit_cg2_mc(&empty_bar[stage], 0b11);   // both CTAs may refill this slot
           if (++stage == kStages) { stage = 0; phase ^= 1; }
@@ -403,8 +425,8 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
       const int n0 = ntile(r) * BNP;
       const int row = m0 + r_in;
-      const int buf = it & 1;
-      const uint32_t buf_phase = (it >> 1) & 1;
+      const int buf = C::kAccBufs == 2 ? (it & 1) : 0;
+      const uint32_t buf_phase = C::kAccBufs == 2 ? ((it >> 1) & 1) : (it & 1);
       mbar_wait(&tmem_full[buf], buf_phase);
       tc_fence_after();
       const uint32_t t_row = tmem_base + lane_off + buf * BNP;
@@ -688,13 +710,25 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stre
   // 256-wide pair tile unless the caller forces 128 (measured slower on every model shape, kept for narrow N)
   int bnp = (a->tile_n == 128 || a->N < 256) ? 128 : 256;
   if (epi == EPI_SWIGLU) bnp = 256;
+  // 384-wide tile when it needs fewer column-waves than the 256-wide one (N = 768: 64 tiles in one wave
+  // instead of 96 tiles in two), for the epilogues it is instantiated with
+  if (bnp == 256 && ag == nullptr && !a_mn && a->N % 384 == 0 && a->split_k <= 1 &&
+      (epi == EPI_BF16 || (epi == EPI_RESID_DROPOUT && !b_mn)) && a->tile_n != 256) {
+    int hw = sm_count();
+    if (a->max_ctas > 0 && a->max_ctas < hw) hw = a->max_ctas;
+    const long hw_pairs = hw / 2 > 0 ? hw / 2 : 1;
+    const long tm = (a->M + 2 * BM - 1) / (2 * BM);
+    const long cost256 = ((tm * ((a->N + 255) / 256) + hw_pairs - 1) / hw_pairs) * 256;
+    const long cost384 = ((tm * (a->N / 384) + hw_pairs - 1) / hw_pairs) * 384;
+    if (a->tile_n == 384 || cost384 < cost256) bnp = 384;
+  }
 
   CUtensorMap ta, tb, tc, tx;
   int rc;
   if (!a_mn) rc = make_tmap_2d_bf16(&ta, a->A, a->K, a->M, a->lda, 64, BM);
   else       rc = make_tmap_2d_bf16(&ta, a->A, a->M, a->K, a->lda, 64, BK);
   if (rc) return rc;
-  if (!b_mn) rc = make_tmap_2d_bf16(&tb, a->B, a->K, a->N, a->ldb, 64, bnp / 2);
+  if (!b_mn) rc = make_tmap_2d_bf16(&tb, a->B, a->K, a->N, a->ldb, 64, bnp == 384 ? 64 : bnp / 2);   // 384: three 64-row chunks
   else       rc = make_tmap_2d_bf16(&tb, a->B, a->N, a->K, a->ldb, 64, BK);
   if (rc) return rc;
   const int c_cols = epi == EPI_SWIGLU_BWD ? 2 * a->half_n : a->N;   // SwiGLU': C = [dgate | dup] is 2*half_n wide
@@ -756,6 +790,11 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stre
   }
   const int grid = int(pairs * 2);
   if (epi == EPI_SWIGLU) return dispatch<256, EPI_SWIGLU>(a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
+  if (bnp == 384) {
+    if (epi == EPI_RESID_DROPOUT) return launch<384, false, false, EPI_RESID_DROPOUT>(ta, tb, tc, tx, p, grid, stream);
+    if (b_mn) return launch<384, false, true, EPI_BF16>(ta, tb, tc, tx, p, grid, stream);
+    return launch<384, false, false, EPI_BF16>(ta, tb, tc, tx, p, grid, stream);
+  }
   if (bnp == 256) return dispatch_epi<256>(epi, a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
   return dispatch_epi<128>(epi, a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
 }

@@ -69,3 +69,40 @@ def test_gemm2_vocab_like_ragged_m_and_padded_ld():
     k.gemm(dlogits, x, g, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, M=V, K=rows, pair=True)
     torch.cuda.synchronize()
     _check(g, dlogits[:, :V].float().t() @ x.float(), rows, "pair dW ragged")
+
+
+@pytest.mark.parametrize("b_mn", [False, True])
+@pytest.mark.parametrize("M,N,K", [(8192, 768, 768), (1000, 768, 320), (512, 1536, 3072)])
+def test_gemm2_tile384(b_mn, M, N, K):
+    """384-wide pair tile (two MMAs per K step, single accumulator): forced here, and chosen by the
+    launcher itself for N = 768 problems."""
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    torch.manual_seed(3)
+    a = _mk((M, K))
+    b = _mk((K, N) if b_mn else (N, K))
+    ref = _ref(a, b, False, b_mn)
+    for tile_n in (384, 0):
+        c = torch.full((M, N), float("nan"), device="cuda", dtype=torch.bfloat16)
+        k.gemm(a, b, c, b_mn=b_mn, pair=True, tile_n=tile_n)
+        torch.cuda.synchronize()
+        _check(c, ref, K, f"tile384 tile_n={tile_n} b_mn={b_mn} {M}x{N}x{K}")
+
+
+def test_gemm2_tile384_resid_dropout():
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    torch.manual_seed(4)
+    M, N, K, p = 2048, 768, 3072, 0.1
+    a, b = _mk((M, K), 0.5), _mk((N, K), 0.05)
+    res = torch.randn(M, N, device="cuda")
+    rng = torch.tensor([77, 5], dtype=torch.int64, device="cuda")
+    mask = torch.zeros(M, N, dtype=torch.uint8, device="cuda")
+    k.dropout_mask(mask, p, rng, 3)
+    ref = res + (a.float() @ b.float().t()) * mask.float() / (1 - p)
+    for tile_n in (384, 256):
+        out = torch.zeros(M, N, device="cuda")
+        k.gemm(a, b, out, epilogue=k.EPI_RESID_DROPOUT, residual=res, dropout_p=p, rng_state=rng, rng_stream=3,
+               pair=True, tile_n=tile_n)
+        torch.cuda.synchronize()
+        _check(out, ref, K, f"tile {tile_n} resid+dropout")
