@@ -83,6 +83,16 @@ def main():
     cases.append(("qkv wgrad", L * MB, lambda: k.gemm(qkv, x, gw_qkv, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, split_k=2)))
     cases.append(("o_proj wgrad", L * MB, lambda: k.gemm(dy, x, gw_o, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, split_k=8)))
 
+    # cuBLAS on the plain-epilogue shapes, for the joules-per-FLOP comparison
+    ref_out = torch.empty(T, h, device="cuda", dtype=torch.bfloat16)
+    cases.append(("cuBLAS gate|up dgrad shape", 0, lambda: torch.matmul(dgu, wgu, out=ref_out)))
+    cases.append(("cuBLAS qkv dgrad shape", 0, lambda: torch.matmul(qkv, wqkv, out=ref_out)))
+    ref_gu = torch.empty(T, 2 * I, device="cuda", dtype=torch.bfloat16)
+    cases.append(("cuBLAS gate|up fwd shape (no swiglu)", 0, lambda: torch.matmul(x, wgu.t(), out=ref_gu)))
+    big_a, big_b, big_c = bf(8192, 8192), bf(8192, 8192), torch.empty(8192, 8192, device="cuda", dtype=torch.bfloat16)
+    cases.append(("cuBLAS 8192^3", 0, lambda: torch.matmul(big_a, big_b.t(), out=big_c)))
+    cases.append(("ours   8192^3", 0, lambda: k.gemm(big_a, big_b, big_c)))
+
     out, lse = torch.zeros(T, h, device="cuda", dtype=torch.bfloat16), torch.zeros(B, Hh, S, device="cuda")
     dqkv, delta, dq = torch.zeros(T, 3 * h, device="cuda", dtype=torch.bfloat16), torch.zeros(B, Hh, S, device="cuda"), torch.empty(T, h, device="cuda")
     qkv_s = bf(T, 3 * h, s=0.8)

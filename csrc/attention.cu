@@ -69,13 +69,14 @@ __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t
 
 // ================================================================================================ forward
 struct FwdSmem {
-  static constexpr int kQ = 0;
-  static constexpr int kK = kQ + kTile;            // 2 stages
+  static constexpr int kQ = 0;                     // 2 buffers (next tile's Q lands while this one finishes)
+  static constexpr int kK = kQ + 2 * kTile;        // 2 stages
   static constexpr int kV = kK + 2 * kTile;        // 2 stages
   static constexpr int kP = kV + 2 * kTile;        // 2 buffers x 32 KB
   static constexpr int kBars = kP + 2 * kPTile;
   static constexpr int kXchg = kBars + 256;                 // float [2][4][128] row-max exchange
-  static constexpr int kTotal = kXchg + 2 * 4 * 128 * 4 + 1024;
+  static constexpr int kXchgL = kXchg + 2 * 4 * 128 * 4;    // float [4][128] row-sum exchange (end of a tile)
+  static constexpr int kTotal = kXchgL + 4 * 128 * 4 + 1024;
 };
 
 constexpr int kSoftmaxWarps = 16;   // four per scheduler: each thread owns one row x 32 score columns
@@ -86,35 +87,47 @@ constexpr int kAttnThreads = 64 + kSoftmaxWarps * 32;
 // barrier per quarter instead of one over all 512 softmax threads.
 __device__ __forceinline__ void softmax_bar_sync(int qd) { asm volatile("bar.sync %0, 128;" ::"r"(qd + 1) : "memory"); }
 
+// Work list of a persistent attention CTA.  Tiles are numbered heaviest first (tile / bh_count = size
+// rank) and dealt to the CTAs in boustrophedon order -- round 0 left to right, round 1 right to left, ... --
+// which for causal tile sizes 8,7,..,1 x 96 on 148 CTAs gives every CTA 21..24 kv blocks (mean 23.4), as
+// good as a greedy scheduler and with no atomics, barrier re-initialisation or TMEM re-allocation
+// between tiles.  Returns the tile index of this CTA's round r, or -1 when that slot is past the end.
+__device__ __forceinline__ int snake_tile(int r, int total) {
+  const int P = int(gridDim.x), c = int(blockIdx.x);
+  const int idx = r * P + ((r & 1) ? P - 1 - c : c);
+  return idx < total ? idx : -1;
+}
+
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::kBars);
-  uint64_t* q_full = bars;            // 1
-  uint64_t* k_full = bars + 1;        // 2
-  uint64_t* k_empty = bars + 3;       // 2
-  uint64_t* v_full = bars + 5;        // 2
-  uint64_t* v_empty = bars + 7;       // 2
-  uint64_t* s_full = bars + 9;        // 2
-  uint64_t* s_free = bars + 11;       // 2 (count 4)
-  uint64_t* p_ready = bars + 13;      // 2 (count 4)
-  uint64_t* o_full = bars + 15;       // 2
-  uint64_t* o_free = bars + 17;       // 2 (count 4)
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 19);
+  uint64_t* q_full = bars;            // 2
+  uint64_t* q_empty = bars + 2;       // 2
+  uint64_t* k_full = bars + 4;        // 2
+  uint64_t* k_empty = bars + 6;       // 2
+  uint64_t* v_full = bars + 8;        // 2
+  uint64_t* v_empty = bars + 10;      // 2
+  uint64_t* s_full = bars + 12;       // 2
+  uint64_t* s_free = bars + 14;       // 2 (count = softmax warps)
+  uint64_t* p_ready = bars + 16;      // 2 (count = softmax warps)
+  uint64_t* o_full = bars + 18;       // 2
+  uint64_t* o_free = bars + 20;       // 2 (count = softmax warps)
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 22);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + kBlk - 1) / kBlk;
-  const int qi = nq - 1 - blockIdx.x;  // heavy (long) rows first
-  const int hd = blockIdx.y, b = blockIdx.z;
+  const int bh_count = p.H * p.B;
+  const int total = nq * bh_count;
+  const int rounds = (total + int(gridDim.x) - 1) / int(gridDim.x);
   const int h = p.H * kD;
-  const int nkv = qi + 1;
-  const int row_base = b * p.S;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_qkv);
-    mbar_init(q_full, 1);
     for (int i = 0; i < 2; ++i) {
+      mbar_init(&q_full[i], 1);
+      mbar_init(&q_empty[i], 1);
       mbar_init(&k_full[i], 1);
       mbar_init(&k_empty[i], 1);
       mbar_init(&v_full[i], 1);
@@ -135,30 +148,41 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
   const uint32_t tS[2] = {tmem + 0, tmem + 128};
   const uint32_t tO[2] = {tmem + 256, tmem + 320};
 
+  // Every role walks the same tile list; `ti` counts this CTA's tiles (Q buffer / phase) and `G` its kv
+  // blocks across tiles (K/V stages, S/P/O buffers and their phases), so no barrier is ever re-armed.
   if (warp == 0) {
     if (lane == 0) {
-      mbar_expect_tx(q_full, kTile);
-      tma_load_2d(smem + FwdSmem::kQ, &tm_qkv, q_full, hd * kD, row_base + qi * kBlk);
-      for (int j = 0; j < nkv; ++j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
-        mbar_wait(&k_empty[st], ph ^ 1);
-        mbar_expect_tx(&k_full[st], kTile);
-        tma_load_2d(smem + FwdSmem::kK + st * kTile, &tm_qkv, &k_full[st], h + hd * kD, row_base + j * kBlk);
-        mbar_wait(&v_empty[st], ph ^ 1);
-        mbar_expect_tx(&v_full[st], kTile);
-        tma_load_2d(smem + FwdSmem::kV + st * kTile, &tm_qkv, &v_full[st], 2 * h + hd * kD, row_base + j * kBlk);
+      uint32_t G = 0;
+      int ti = 0;
+      for (int r = 0; r < rounds; ++r) {
+        const int tile = snake_tile(r, total);
+        if (tile < 0) continue;
+        const int qi = nq - 1 - tile / bh_count, bh = tile % bh_count;
+        const int hd = bh % p.H, row_base = (bh / p.H) * p.S;
+        const int qb = ti & 1;
+        mbar_wait(&q_empty[qb], ((ti >> 1) & 1) ^ 1);
+        mbar_expect_tx(&q_full[qb], kTile);
+        tma_load_2d(smem + FwdSmem::kQ + qb * kTile, &tm_qkv, &q_full[qb], hd * kD, row_base + qi * kBlk);
+        for (int j = 0; j <= qi; ++j, ++G) {
+          const int st = G & 1;
+          const uint32_t ph = (G >> 1) & 1;
+          mbar_wait(&k_empty[st], ph ^ 1);
+          mbar_expect_tx(&k_full[st], kTile);
+          tma_load_2d(smem + FwdSmem::kK + st * kTile, &tm_qkv, &k_full[st], h + hd * kD, row_base + j * kBlk);
+          mbar_wait(&v_empty[st], ph ^ 1);
+          mbar_expect_tx(&v_full[st], kTile);
+          tma_load_2d(smem + FwdSmem::kV + st * kTile, &tm_qkv, &v_full[st], 2 * h + hd * kD, row_base + j * kBlk);
+        }
+        ++ti;
       }
     }
   } else if (warp == 1) {
     if (lane == 0) {
       constexpr uint32_t idesc_s = make_idesc_bf16(128, 128, false, false);
       constexpr uint32_t idesc_o = make_idesc_bf16(128, 64, false, true);
-      const uint32_t q_addr = smem_u32(smem + FwdSmem::kQ);
-      mbar_wait(q_full, 0);
-      auto issue_s = [&](int j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
+      auto issue_s = [&](uint32_t g, uint32_t q_addr) {
+        const int st = g & 1;
+        const uint32_t ph = (g >> 1) & 1;
         mbar_wait(&k_full[st], ph);
         mbar_wait(&s_free[st], ph ^ 1);
         tc_fence_after();
@@ -170,9 +194,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         tc_commit(&k_empty[st]);
         tc_commit(&s_full[st]);
       };
-      auto issue_pv = [&](int j) {
-        const int st = j & 1;
-        const uint32_t ph = (j >> 1) & 1;
+      auto issue_pv = [&](uint32_t g) {
+        const int st = g & 1;
+        const uint32_t ph = (g >> 1) & 1;
         mbar_wait(&p_ready[st], ph);
         mbar_wait(&v_full[st], ph);
         mbar_wait(&o_free[st], ph ^ 1);
@@ -186,124 +210,149 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         tc_commit(&v_empty[st]);
         tc_commit(&o_full[st]);
       };
-      issue_s(0);
-      for (int j = 0; j < nkv; ++j) {
-        if (j + 1 < nkv) issue_s(j + 1);
-        issue_pv(j);
+      uint32_t G = 0;
+      int ti = 0;
+      for (int r = 0; r < rounds; ++r) {
+        const int tile = snake_tile(r, total);
+        if (tile < 0) continue;
+        const int nkv = nq - tile / bh_count;   // = qi + 1
+        const int qb = ti & 1;
+        const uint32_t q_addr = smem_u32(smem + FwdSmem::kQ + qb * kTile);
+        mbar_wait(&q_full[qb], (ti >> 1) & 1);
+        issue_s(G, q_addr);
+        for (int j = 0; j < nkv; ++j) {
+          if (j + 1 < nkv) issue_s(G + j + 1, q_addr);
+          else tc_commit(&q_empty[qb]);          // every S MMA of this tile has been issued: Q may be replaced
+          issue_pv(G + j);
+        }
+        G += nkv;
+        ++ti;
       }
     }
   } else {
     const int qd = warp & 3;
     const int qt = (warp - 2) >> 2;               // which 32-column quarter of the score tile this thread owns
     const int r = qd * 32 + lane;                 // row within the q tile
-    const int qrow = qi * kBlk + r;               // position in the sequence
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
     const uint32_t thresh_hi = dropout_threshold16(p.p_drop) << 16;
+    const float inv_keep = drop ? 1.f / (1.f - p.p_drop) : 1.f;
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
-    const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
-    float* xchg = reinterpret_cast<float*>(smem + FwdSmem::kXchg);   // [2][4][128]
+    float* xchg = reinterpret_cast<float*>(smem + FwdSmem::kXchg);     // [2][4][128]
+    float* xchg_l = reinterpret_cast<float*>(smem + FwdSmem::kXchgL);  // [4][128]
 
-    float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
-    float o[16];
-#pragma unroll
-    for (int e = 0; e < 16; ++e) o[e] = 0.f;
+    uint32_t G = 0;
+    for (int rr = 0; rr < rounds; ++rr) {
+      const int tile = snake_tile(rr, total);
+      if (tile < 0) continue;
+      const int qi = nq - 1 - tile / bh_count, bh = tile % bh_count;
+      const int hd = bh % p.H, b = bh / p.H;
+      const int nkv = qi + 1;
+      const int row_base = b * p.S;
+      const int qrow = qi * kBlk + r;               // position in the sequence
+      const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S8;
 
-    auto fold_o = [&](int pb, uint32_t parity, float alpha) {
-      mbar_wait(&o_full[pb], parity);
-      tc_fence_after();
-      uint32_t v[16];
-      __syncwarp();
-      tmem_ld_32x32b_x16(tO[pb] + lane_off + qt * 16, v);
-      tmem_ld_wait();
+      float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
+      float o[16];
 #pragma unroll
-      for (int e = 0; e < 16; ++e) o[e] = o[e] * alpha + __uint_as_float(v[e]);
-    };
+      for (int e = 0; e < 16; ++e) o[e] = 0.f;
 
-    for (int j = 0; j < nkv; ++j) {
-      const int st = j & 1;
-      const uint32_t ph = (j >> 1) & 1;
-      const bool diag = (j == qi);
-      mbar_wait(&s_full[st], ph);
-      tc_fence_after();
-      // this thread's 32 scores stay in registers for both the max and the exp pass
-      uint32_t v[32];
-      __syncwarp();
-      tmem_ld_32x32b_x32(tS[st] + lane_off + qt * 32, v);
-      tmem_ld_wait();
-      // The causal mask only touches the diagonal tile: a warp-uniform branch keeps the compare +
-      // select out of every other tile.  Scores stay raw (unscaled) -- the 1/sqrt(d) * log2(e) factor
-      // is folded into the exponent's FFMA below, and max commutes with a positive scale.
-      if (diag) {
+      auto fold_o = [&](uint32_t g, float alpha) {
+        const int pb = g & 1;
+        mbar_wait(&o_full[pb], (g >> 1) & 1);
+        tc_fence_after();
+        uint32_t v[16];
+        __syncwarp();
+        tmem_ld_32x32b_x16(tO[pb] + lane_off + qt * 16, v);
+        tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 32; ++e)
-          if ((qt * 32 + e) > r) v[e] = 0xFF800000u;   // -inf
-      }
-      float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains instead of one serial max
-#pragma unroll
-      for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], __uint_as_float(v[e]));
-      float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
-      xchg[(st * 4 + qt) * 128 + r] = mx;
-      softmax_bar_sync(qd);
-#pragma unroll
-      for (int t = 0; t < 4; ++t) mx = fmaxf(mx, xchg[(st * 4 + t) * 128 + r]);
-      mx = fmaxf(mx, m);
-      const float m_use = (mx == -INFINITY) ? 0.f : mx;   // m, m_use: running max of the RAW scores
-      const float alpha = ex2_ftz((m - m_use) * kScale2);
-      const float neg_msc = -m_use * kScale2;
-      // probabilities -> smem (bf16, dropout applied, unnormalised)
-      const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + (qt >> 1) * kTile;
-      float l4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        float pv[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          // one FFMA + one MUFU per element; masked entries are ex2(-inf) = 0
-          pv[e] = ex2_ftz(fmaf(__uint_as_float(v[g * 8 + e]), kScale2, neg_msc));
-          l4[e & 3] += pv[e];
-        }
-        if (drop)
-          dropout_zero8(dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3)),
-                        thresh_hi, pv);
-        st_shared_v4(swz(sub, r, (qt & 1) * 4 + g), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
-                     pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
-      }
-      l = l * alpha + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
-      tc_fence_before();
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        mbar_arrive(&p_ready[st]);
-        mbar_arrive(&s_free[st]);
-      }
-      // fold in O_{j-1}
-      if (j > 0) {
-        const int pb = (j - 1) & 1;
-        fold_o(pb, ((j - 1) >> 1) & 1, alpha_prev);
+        for (int e = 0; e < 16; ++e) o[e] = o[e] * alpha + __uint_as_float(v[e]);
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&o_free[pb]);
-      }
-      alpha_prev = alpha;
-      m = m_use;
-    }
-    fold_o((nkv - 1) & 1, ((nkv - 1) >> 1) & 1, alpha_prev);
-    // total row sum = the four column-quarters' partial sums (same running max on all four threads)
-    softmax_bar_sync(qd);
-    xchg[qt * 128 + r] = l;
-    softmax_bar_sync(qd);
-    l = (xchg[r] + xchg[128 + r]) + (xchg[256 + r] + xchg[384 + r]);
-    if (qrow < p.S) {
-      const float inv = (drop ? 1.f / (1.f - p.p_drop) : 1.f) / l;
-      __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD + qt * 16;
+      };
+
+      for (int j = 0; j < nkv; ++j) {
+        const uint32_t g = G + j;
+        const int st = g & 1;
+        const uint32_t ph = (g >> 1) & 1;
+        const bool diag = (j == qi);
+        mbar_wait(&s_full[st], ph);
+        tc_fence_after();
+        // this thread's 32 scores stay in registers for both the max and the exp pass
+        uint32_t v[32];
+        __syncwarp();
+        tmem_ld_32x32b_x32(tS[st] + lane_off + qt * 32, v);
+        tmem_ld_wait();
+        // The causal mask only touches the diagonal tile: a warp-uniform branch keeps the compare +
+        // select out of every other tile.  Scores stay raw (unscaled) -- the 1/sqrt(d) * log2(e) factor
+        // is folded into the exponent's FFMA below, and max commutes with a positive scale.
+        if (diag) {
 #pragma unroll
-      for (int g = 0; g < 2; ++g)
-        *reinterpret_cast<uint4*>(dst + g * 8) =
-            make_uint4(pack_bf16x2(o[g * 8 + 0] * inv, o[g * 8 + 1] * inv), pack_bf16x2(o[g * 8 + 2] * inv, o[g * 8 + 3] * inv),
-                       pack_bf16x2(o[g * 8 + 4] * inv, o[g * 8 + 5] * inv), pack_bf16x2(o[g * 8 + 6] * inv, o[g * 8 + 7] * inv));
-      if (qt == 0) p.lse[size_t(b * p.H + hd) * p.S + qrow] = m * kScale2 + log2f(l);
+          for (int e = 0; e < 32; ++e)
+            if ((qt * 32 + e) > r) v[e] = 0xFF800000u;   // -inf
+        }
+        float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};   // four chains instead of one serial max
+#pragma unroll
+        for (int e = 0; e < 32; ++e) mx4[e & 3] = fmaxf(mx4[e & 3], __uint_as_float(v[e]));
+        float mx = fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3]));
+        xchg[(st * 4 + qt) * 128 + r] = mx;
+        softmax_bar_sync(qd);
+#pragma unroll
+        for (int t = 0; t < 4; ++t) mx = fmaxf(mx, xchg[(st * 4 + t) * 128 + r]);
+        mx = fmaxf(mx, m);
+        const float m_use = (mx == -INFINITY) ? 0.f : mx;   // m, m_use: running max of the RAW scores
+        const float alpha = ex2_ftz((m - m_use) * kScale2);
+        const float neg_msc = -m_use * kScale2;
+        // probabilities -> smem (bf16, dropout applied, unnormalised)
+        const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + (qt >> 1) * kTile;
+        float l4[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          float pv[8];
+#pragma unroll
+          for (int e = 0; e < 8; ++e) {
+            // one FFMA + one MUFU per element; masked entries are ex2(-inf) = 0
+            pv[e] = ex2_ftz(fmaf(__uint_as_float(v[gq * 8 + e]), kScale2, neg_msc));
+            l4[e & 3] += pv[e];
+          }
+          if (drop)
+            dropout_zero8(dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + gq * 8) >> 3)),
+                          thresh_hi, pv);
+          st_shared_v4(swz(sub, r, (qt & 1) * 4 + gq), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
+                       pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
+        }
+        l = l * alpha + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          mbar_arrive(&p_ready[st]);
+          mbar_arrive(&s_free[st]);
+        }
+        if (j > 0) fold_o(g - 1, alpha_prev);   // fold in O_{j-1}
+        alpha_prev = alpha;
+        m = m_use;
+      }
+      fold_o(G + nkv - 1, alpha_prev);
+      G += nkv;
+      // total row sum = the four column-quarters' partial sums (same running max on all four threads)
+      xchg_l[qt * 128 + r] = l;
+      softmax_bar_sync(qd);
+      l = (xchg_l[r] + xchg_l[128 + r]) + (xchg_l[256 + r] + xchg_l[384 + r]);
+      if (qrow < p.S) {
+        const float inv = inv_keep / l;
+        __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD + qt * 16;
+#pragma unroll
+        for (int gq = 0; gq < 2; ++gq)
+          *reinterpret_cast<uint4*>(dst + gq * 8) =
+              make_uint4(pack_bf16x2(o[gq * 8 + 0] * inv, o[gq * 8 + 1] * inv), pack_bf16x2(o[gq * 8 + 2] * inv, o[gq * 8 + 3] * inv),
+                         pack_bf16x2(o[gq * 8 + 4] * inv, o[gq * 8 + 5] * inv), pack_bf16x2(o[gq * 8 + 6] * inv, o[gq * 8 + 7] * inv));
+        if (qt == 0) p.lse[size_t(bh) * p.S + qrow] = m * kScale2 + log2f(l);
+      }
+      // the row-sum slots are rewritten by the next tile only after its own kv loop, which contains
+      // at least one quarter-wide barrier: no thread can still be reading this tile's sums by then
     }
   }
 
@@ -384,8 +433,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + kBlk - 1) / kBlk;
-  const int j = blockIdx.x;  // kv block (small j = most q blocks = heaviest, scheduled first)
-  const int hd = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, heaviest kv blocks (small j = most q blocks) first across the whole grid
+  const int bh_count = p.H * p.B;
+  const int j = int(blockIdx.x) / bh_count;
+  const int hd = (int(blockIdx.x) % bh_count) % p.H, b = (int(blockIdx.x) % bh_count) / p.H;
   const int h = p.H * kD;
   const int niter = nq - j;
   const int row_base = b * p.S;
@@ -647,7 +698,9 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::kTotal));
     configured = true;
   }
-  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  // persistent: one CTA per SM walks its share of the (q tile, head, batch) list
+  const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;
+  dim3 grid(tiles < sm_count() ? tiles : sm_count());
   attn_fwd_kernel<<<grid, kAttnThreads, FwdSmem::kTotal, STREAM(stream)>>>(tm, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
@@ -679,7 +732,7 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal));
     configured = true;
   }
-  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  dim3 grid(((seq + kBlk - 1) / kBlk) * heads * batch);
   attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);
@@ -785,7 +838,7 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
-  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  dim3 grid(((seq + kBlk - 1) / kBlk) * heads * batch);
   attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);

@@ -73,8 +73,12 @@ attn_fwd2_kernel(const __grid_constant__ CUtensorMap tm_qkv, const Params p) {
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + kBlk - 1) / kBlk;
-  const int qi = nq - 1 - blockIdx.x;   // long rows first
-  const int hd = blockIdx.y, b = blockIdx.z;
+  // 1-D grid, longest rows first ACROSS the whole grid (blocks are issued in index order): every
+  // (batch, head) pair's 8-block tile starts before any 7-block tile, ... so the tail of the kernel is
+  // made of the one-block tiles instead of whichever heavy tiles happened to come last.
+  const int bh_count = p.H * p.B;
+  const int qi = nq - 1 - int(blockIdx.x) / bh_count;
+  const int hd = (int(blockIdx.x) % bh_count) % p.H, b = (int(blockIdx.x) % bh_count) / p.H;
   const int h = p.H * kD;
   const int nkv = qi + 1;
   const int row_base = b * p.S;
@@ -295,7 +299,7 @@ extern "C" int b200_attn_fwd2(const void* qkv, void* out, float* lse, int batch,
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::kTotal));
     configured = true;
   }
-  dim3 grid((seq + kBlk - 1) / kBlk, heads, batch);
+  dim3 grid(((seq + kBlk - 1) / kBlk) * heads * batch);
   attn_fwd2_kernel<<<grid, kThreads, Smem::kTotal, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
