@@ -414,6 +414,10 @@ struct BwdSmem {
 };
 static_assert(BwdSmem::kTotal <= 227 * 1024, "backward smem exceeds the 227 KB per-CTA limit");
 
+// Persistent: one CTA per SM walks its boustrophedon share of the (kv block, head, batch) list (see
+// snake_tile), heaviest kv blocks (small j = most q blocks) first.  `ti` counts this CTA's tiles and `I`
+// its (kv block, q block) pairs across tiles; every ring / buffer index and mbarrier phase derives from
+// those two counters, so nothing is re-initialised between tiles.
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
                 const AttnParams p) {
@@ -421,30 +425,30 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::kBars);
   uint64_t* kv_full = bars;            // 1
-  uint64_t* qdo_full = bars + 1;       // 2
-  uint64_t* qdo_empty = bars + 3;      // 2
-  uint64_t* sdp_full = bars + 5;       // 1
-  uint64_t* s_free = bars + 6;         // 1 (count 4)
-  uint64_t* pds_ready = bars + 7;      // 2 (count = softmax warps)
-  uint64_t* dq_full = bars + 9;        // 2
-  uint64_t* dq_free = bars + 11;       // 2 (count = softmax warps)
-  uint64_t* acc_full = bars + 13;      // 1
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 14);
+  uint64_t* kv_empty = bars + 1;       // 1  every MMA of the tile has completed: K / V may be replaced
+  uint64_t* qdo_full = bars + 2;       // 2
+  uint64_t* qdo_empty = bars + 4;      // 2
+  uint64_t* sdp_full = bars + 6;       // 1
+  uint64_t* s_free = bars + 7;         // 1 (count = softmax warps)
+  uint64_t* pds_ready = bars + 8;      // 2 (count = softmax warps)
+  uint64_t* dq_full = bars + 10;       // 2
+  uint64_t* dq_free = bars + 12;       // 2 (count = softmax warps)
+  uint64_t* acc_full = bars + 14;      // 1
+  uint64_t* acc_free = bars + 15;      // 1 (count = softmax warps): dK / dV have been read out of TMEM
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + kBlk - 1) / kBlk;
-  // 1-D grid, heaviest kv blocks (small j = most q blocks) first across the whole grid
   const int bh_count = p.H * p.B;
-  const int j = int(blockIdx.x) / bh_count;
-  const int hd = (int(blockIdx.x) % bh_count) % p.H, b = (int(blockIdx.x) % bh_count) / p.H;
+  const int total = nq * bh_count;
+  const int rounds = (total + int(gridDim.x) - 1) / int(gridDim.x);
   const int h = p.H * kD;
-  const int niter = nq - j;
-  const int row_base = b * p.S;
 
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     mbar_init(kv_full, 1);
+    mbar_init(kv_empty, 1);
     for (int i = 0; i < 2; ++i) {
       mbar_init(&qdo_full[i], 1);
       mbar_init(&qdo_empty[i], 1);
@@ -457,6 +461,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       mbar_init(&dq_free[i], kSoftmaxWarps);
     }
     mbar_init(acc_full, 1);
+    mbar_init(acc_free, kSoftmaxWarps);
     fence_barrier_init();
   }
   if (warp == 1) tmem_alloc<512>(tmem_ptr);
@@ -468,16 +473,25 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 
   if (warp == 0) {
     if (lane == 0) {
-      mbar_expect_tx(kv_full, 2 * kTile);
-      tma_load_2d(smem + BwdSmem::kK, &tm_qkv, kv_full, h + hd * kD, row_base + j * kBlk);
-      tma_load_2d(smem + BwdSmem::kV, &tm_qkv, kv_full, 2 * h + hd * kD, row_base + j * kBlk);
-      for (int it = 0; it < niter; ++it) {
-        const int st = it & 1;
-        const uint32_t ph = (it >> 1) & 1;
-        mbar_wait(&qdo_empty[st], ph ^ 1);
-        mbar_expect_tx(&qdo_full[st], 2 * kTile);
-        tma_load_2d(smem + BwdSmem::kQ + st * kTile, &tm_qkv, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
-        tma_load_2d(smem + BwdSmem::kdO + st * kTile, &tm_do, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
+      uint32_t I = 0;
+      int ti = 0;
+      for (int r = 0; r < rounds; ++r) {
+        const int tile = snake_tile(r, total);
+        if (tile < 0) continue;
+        const int j = tile / bh_count, bh = tile % bh_count;
+        const int hd = bh % p.H, row_base = (bh / p.H) * p.S;
+        mbar_wait(kv_empty, (ti & 1) ^ 1);
+        mbar_expect_tx(kv_full, 2 * kTile);
+        tma_load_2d(smem + BwdSmem::kK, &tm_qkv, kv_full, h + hd * kD, row_base + j * kBlk);
+        tma_load_2d(smem + BwdSmem::kV, &tm_qkv, kv_full, 2 * h + hd * kD, row_base + j * kBlk);
+        for (int it = 0; it < nq - j; ++it, ++I) {
+          const int st = I & 1;
+          mbar_wait(&qdo_empty[st], ((I >> 1) & 1) ^ 1);
+          mbar_expect_tx(&qdo_full[st], 2 * kTile);
+          tma_load_2d(smem + BwdSmem::kQ + st * kTile, &tm_qkv, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
+          tma_load_2d(smem + BwdSmem::kdO + st * kTile, &tm_do, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
+        }
+        ++ti;
       }
     }
   } else if (warp == 1) {
@@ -487,15 +501,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       constexpr uint32_t idesc_dq = make_idesc_bf16(128, 64, false, true);     // dS K
       const uint32_t k_addr = smem_u32(smem + BwdSmem::kK), v_addr = smem_u32(smem + BwdSmem::kV);
       const uint32_t p_addr = smem_u32(smem + BwdSmem::kP), ds_addr = smem_u32(smem + BwdSmem::kdS);
-      mbar_wait(kv_full, 0);
-      // S = Q K^T and dP = dO V^T of q block `it` (one TMEM buffer each; the element-wise warps free
-      // it as soon as both are in registers, so block it+1's pair runs under block it's softmax).
-      auto issue_sdp = [&](int it) {
-        const int st = it & 1;
+      // S = Q K^T and dP = dO V^T of pair I (one TMEM buffer each; the element-wise warps free it as soon
+      // as both are in registers, so the next pair's S / dP run under this pair's softmax).
+      auto issue_sdp = [&](uint32_t I) {
+        const int st = I & 1;
         const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
         const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
-        mbar_wait(&qdo_full[st], (it >> 1) & 1);
-        mbar_wait(s_free, (it & 1) ^ 1);
+        mbar_wait(&qdo_full[st], (I >> 1) & 1);
+        mbar_wait(s_free, (I & 1) ^ 1);
         tc_fence_after();
 #pragma unroll
         for (int t = 0; t < 4; ++t)
@@ -507,33 +520,46 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
                        idesc_s, t > 0);
         tc_commit(sdp_full);
       };
-      issue_sdp(0);
-      for (int it = 0; it < niter; ++it) {
-        const int st = it & 1;                 // Q/dO stage, P/dS buffer and dQ buffer of this block
-        const uint32_t use = (it >> 1) & 1;
-        const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
-        const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
-        const uint32_t pb = p_addr + st * kPTile, dsb = ds_addr + st * kPTile;
-        if (it + 1 < niter) issue_sdp(it + 1);
-        mbar_wait(&pds_ready[st], use);
-        mbar_wait(&dq_free[st], use ^ 1);
-        tc_fence_after();
+      uint32_t I0 = 0;
+      int ti = 0;
+      for (int r = 0; r < rounds; ++r) {
+        const int tile = snake_tile(r, total);
+        if (tile < 0) continue;
+        const int niter = nq - tile / bh_count;
+        mbar_wait(kv_full, ti & 1);
+        issue_sdp(I0);
+        mbar_wait(acc_free, (ti & 1) ^ 1);     // previous tile's dK / dV have left TMEM
+        for (int it = 0; it < niter; ++it) {
+          const uint32_t I = I0 + it;
+          const int st = I & 1;                 // Q/dO stage, P/dS buffer and dQ buffer of this pair
+          const uint32_t use = (I >> 1) & 1;
+          const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
+          const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
+          const uint32_t pb = p_addr + st * kPTile, dsb = ds_addr + st * kPTile;
+          if (it + 1 < niter) issue_sdp(I + 1);
+          mbar_wait(&pds_ready[st], use);
+          mbar_wait(&dq_free[st], use ^ 1);
+          tc_fence_after();
 #pragma unroll
-        for (int t = 0; t < 8; ++t)  // dV += P~^T dO   (K = 128 q rows, 16 per step)
-          umma_bf16_ss(tdV, make_smem_desc_sw128(pb + t * 2048, kTile, 1024),
-                       make_smem_desc_sw128(do_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
+          for (int t = 0; t < 8; ++t)  // dV += P~^T dO   (K = 128 q rows, 16 per step)
+            umma_bf16_ss(tdV, make_smem_desc_sw128(pb + t * 2048, kTile, 1024),
+                         make_smem_desc_sw128(do_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
 #pragma unroll
-        for (int t = 0; t < 8; ++t)  // dK += dS^T Q
-          umma_bf16_ss(tdK, make_smem_desc_sw128(dsb + t * 2048, kTile, 1024),
-                       make_smem_desc_sw128(q_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
+          for (int t = 0; t < 8; ++t)  // dK += dS^T Q
+            umma_bf16_ss(tdK, make_smem_desc_sw128(dsb + t * 2048, kTile, 1024),
+                         make_smem_desc_sw128(q_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
 #pragma unroll
-        for (int t = 0; t < 8; ++t)  // dQ_i = dS K     (K = 128 kv, 16 per step)
-          umma_bf16_ss(tdQ + st * 64, make_smem_desc_sw128(dsb + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
-                       make_smem_desc_sw128(k_addr + t * 2048, kTile, 1024), idesc_dq, t > 0);
-        tc_commit(&qdo_empty[st]);
-        tc_commit(&dq_full[st]);
+          for (int t = 0; t < 8; ++t)  // dQ_i = dS K     (K = 128 kv, 16 per step)
+            umma_bf16_ss(tdQ + st * 64, make_smem_desc_sw128(dsb + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
+                         make_smem_desc_sw128(k_addr + t * 2048, kTile, 1024), idesc_dq, t > 0);
+          tc_commit(&qdo_empty[st]);
+          tc_commit(&dq_full[st]);
+        }
+        tc_commit(acc_full);
+        tc_commit(kv_empty);
+        I0 += niter;
+        ++ti;
       }
-      tc_commit(acc_full);
     }
   } else {
     const int qd = warp & 3;
@@ -549,121 +575,146 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const uint32_t p_sub0 = smem_u32(smem + BwdSmem::kP) + (qt >> 1) * kTile;
     const uint32_t ds_sub0 = smem_u32(smem + BwdSmem::kdS) + (qt >> 1) * kTile;
 
-    auto drain_dq = [&](int it) {
-      const int qrow = (j + it) * kBlk + r;
-      mbar_wait(&dq_full[it & 1], (it >> 1) & 1);
-      tc_fence_after();
-      float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + qt * 16;
-      uint32_t v[16];
-      __syncwarp();
-      tmem_ld_32x32b_x16(tdQ + (it & 1) * 64 + lane_off + qt * 16, v);
-      tmem_ld_wait();
-      if (qrow < p.S) {
-#pragma unroll
-        for (int g = 0; g < 4; ++g)
-          asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 4),
-                       "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
-                       "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
-                       : "memory");
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&dq_free[it & 1]);
-    };
+    uint32_t I0 = 0;
+    int ti = 0;
+    for (int rr = 0; rr < rounds; ++rr) {
+      const int tile = snake_tile(rr, total);
+      if (tile < 0) continue;
+      const int j = tile / bh_count, bh = tile % bh_count;
+      const int hd = bh % p.H, row_base = (bh / p.H) * p.S;
+      const int niter = nq - j;
 
-    // Block `it` writes P~/dS buffer it&1; the MMAs of block it-2 that read it have completed because
-    // dQ(it-2) was drained (dq_full covers every earlier MMA) during block it-1.  The drain of dQ(it-1)
-    // comes AFTER this block's element-wise work so its MMAs run underneath that work.
-    // per-row statistics are fetched one block ahead so their global-load latency hides under the math
-    const float* lse_bh = p.lse + size_t(b * p.H + hd) * p.S;
-    const float* delta_bh = p.delta + size_t(b * p.H + hd) * p.S;
-    float lse_nx = 0.f, dl_nx = 0.f;
-    if (j * kBlk + r < p.S) { lse_nx = lse_bh[j * kBlk + r]; dl_nx = delta_bh[j * kBlk + r]; }
-    for (int it = 0; it < niter; ++it) {
-      const int i = j + it;
-      const int qrow = i * kBlk + r;
-      const bool diag = (i == j);
-      const bool row_ok = qrow < p.S;
-      const float neg_lse = row_ok ? log2_inv_keep - lse_nx : -INFINITY;
-      const float dl = row_ok ? dl_nx : 0.f;
-      if (it + 1 < niter && qrow + kBlk < p.S) { lse_nx = lse_bh[qrow + kBlk]; dl_nx = delta_bh[qrow + kBlk]; }
-      const unsigned long long grp_row = ((unsigned long long)(b * p.H + hd) * p.S + qrow) * p.S8;
-      mbar_wait(sdp_full, it & 1);
-      tc_fence_after();
-      uint32_t sv[32], dv[32];
-      __syncwarp();
-      tmem_ld_32x32b_x32(tS + lane_off + qt * 32, sv);
-      tmem_ld_32x32b_x32(tdP + lane_off + qt * 32, dv);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(s_free);   // S / dP are in registers: the next block's pair may overwrite them
-      const uint32_t p_sub = p_sub0 + (it & 1) * kPTile, ds_sub = ds_sub0 + (it & 1) * kPTile;
-      if (diag) {   // causal mask: only the diagonal tile pays for it (warp-uniform branch)
+      // dQ of pair I (local q block `it`) -> fp32 accumulator in global memory
+      auto drain_dq = [&](uint32_t I, int it) {
+        const int qrow = (j + it) * kBlk + r;
+        mbar_wait(&dq_full[I & 1], (I >> 1) & 1);
+        tc_fence_after();
+        float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + qt * 16;
+        uint32_t v[16];
+        __syncwarp();
+        tmem_ld_32x32b_x16(tdQ + (I & 1) * 64 + lane_off + qt * 16, v);
+        tmem_ld_wait();
+        if (qrow < p.S) {
 #pragma unroll
-        for (int e = 0; e < 32; ++e)
-          if ((qt * 32 + e) > r) sv[e] = 0xFF800000u;   // -inf -> probability 0 -> dS 0
-      }
-      // With q = 1/(1-p):  P~ = keep ? q P : 0  and  dS = P (dP~ - delta) / sqrt(d),  dP~ = keep ? q dP : 0.
-      // Folding q into the exponent gives qP from one FFMA + MUFU, and
-      //   dS = qP * (keep ? dP/sqrt(d) - c : -c),  c = delta (1-p) / sqrt(d)
-      // so an element costs FFMA, MUFU, compare, 2 selects, FFMA, FMUL and its share of two packs.
-      const float neg_c = -dl * keep_scale;
-#pragma unroll
-      for (int g = 0; g < 4; ++g) {
-        uint4 rb = make_uint4(0u, 0u, 0u, 0u);   // thresh_hi is 0 without dropout: every lane kept
-        if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3));
-        const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
-        float pd[8], ds[8];
-#pragma unroll
-        for (int e = 0; e < 8; ++e) {
-          const float qp = ex2_ftz(fmaf(__uint_as_float(sv[g * 8 + e]), kScale2, neg_lse));
-          const bool k1 = ((e & 1) ? w[e >> 1] : (w[e >> 1] << 16)) >= thresh_hi;
-          const float t = fmaf(__uint_as_float(dv[g * 8 + e]), kScale, neg_c);
-          ds[e] = qp * (k1 ? t : neg_c);
-          pd[e] = k1 ? qp : 0.f;
+          for (int g = 0; g < 4; ++g)
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 4),
+                         "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
+                         "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
+                         : "memory");
         }
-        const int cc = (qt & 1) * 4 + g;
-        st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
-                     pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
-        st_shared_v4(swz(ds_sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
-                     pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
-      }
-      tc_fence_before();
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(&pds_ready[it & 1]);
-      if (it > 0) drain_dq(it - 1);
-    }
-    drain_dq(niter - 1);
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&dq_free[I & 1]);
+      };
 
-    // dK / dV of this kv block: thread (r, qt) owns kv row r, head-dim columns [16 qt, 16 qt + 16)
-    mbar_wait(acc_full, 0);
-    tc_fence_after();
-    const int kvrow = j * kBlk + r;
-    __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD + qt * 16;
-    __nv_bfloat16* dv_dst = dk_dst + h;
-    {
-      uint32_t kv_[16], vv_[16];
-      __syncwarp();
-      tmem_ld_32x32b_x16(tdK + lane_off + qt * 16, kv_);
-      tmem_ld_32x32b_x16(tdV + lane_off + qt * 16, vv_);
-      tmem_ld_wait();
-      if (kvrow < p.S) {
+      // per-row statistics are fetched one block ahead so their global-load latency hides under the math
+      const float* lse_bh = p.lse + size_t(bh) * p.S;
+      const float* delta_bh = p.delta + size_t(bh) * p.S;
+      float lse_nx = 0.f, dl_nx = 0.f;
+      if (j * kBlk + r < p.S) { lse_nx = lse_bh[j * kBlk + r]; dl_nx = delta_bh[j * kBlk + r]; }
+      // Pair I writes P~/dS buffer I&1; the MMAs of pair I-2 that read it have completed because dQ(I-2)
+      // was drained (dq_full covers every earlier MMA) during pair I-1.  The drain of dQ(I-1) comes AFTER
+      // this pair's element-wise work so its MMAs run underneath that work.
+      for (int it = 0; it < niter; ++it) {
+        const uint32_t I = I0 + it;
+        const int i = j + it;
+        const int qrow = i * kBlk + r;
+        const bool diag = (it == 0);
+        const bool row_ok = qrow < p.S;
+        const float neg_lse = row_ok ? log2_inv_keep - lse_nx : -INFINITY;
+        const float dl = row_ok ? dl_nx : 0.f;
+        if (it + 1 < niter && qrow + kBlk < p.S) { lse_nx = lse_bh[qrow + kBlk]; dl_nx = delta_bh[qrow + kBlk]; }
+        const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S8;
+        mbar_wait(sdp_full, I & 1);
+        tc_fence_after();
+        const uint32_t p_sub = p_sub0 + (I & 1) * kPTile, ds_sub = ds_sub0 + (I & 1) * kPTile;
+        // With q = 1/(1-p):  P~ = keep ? q P : 0  and  dS = P (dP~ - delta) / sqrt(d),  dP~ = keep ? q dP : 0.
+        // Folding q into the exponent gives qP from one FFMA + MUFU, and
+        //   dS = qP * (keep ? dP/sqrt(d) - c : -c),  c = delta (1-p) / sqrt(d)
+        // so an element costs FFMA, MUFU, compare, 2 selects, FFMA, FMUL and its share of two packs.
+        const float neg_c = -dl * keep_scale;
+        // Two halves of 16 columns: 32 live accumulator registers instead of 64 (the kernel is capped at 96
+        // registers per thread by its 18 warps), and the second half's TMEM loads fly under the first's math.
 #pragma unroll
-        for (int g = 0; g < 2; ++g) {
-          *reinterpret_cast<uint4*>(dk_dst + g * 8) = make_uint4(
-              pack_bf16x2(__uint_as_float(kv_[g * 8 + 0]), __uint_as_float(kv_[g * 8 + 1])),
-              pack_bf16x2(__uint_as_float(kv_[g * 8 + 2]), __uint_as_float(kv_[g * 8 + 3])),
-              pack_bf16x2(__uint_as_float(kv_[g * 8 + 4]), __uint_as_float(kv_[g * 8 + 5])),
-              pack_bf16x2(__uint_as_float(kv_[g * 8 + 6]), __uint_as_float(kv_[g * 8 + 7])));
-          *reinterpret_cast<uint4*>(dv_dst + g * 8) = make_uint4(
-              pack_bf16x2(__uint_as_float(vv_[g * 8 + 0]), __uint_as_float(vv_[g * 8 + 1])),
-              pack_bf16x2(__uint_as_float(vv_[g * 8 + 2]), __uint_as_float(vv_[g * 8 + 3])),
-              pack_bf16x2(__uint_as_float(vv_[g * 8 + 4]), __uint_as_float(vv_[g * 8 + 5])),
-              pack_bf16x2(__uint_as_float(vv_[g * 8 + 6]), __uint_as_float(vv_[g * 8 + 7])));
+        for (int hh = 0; hh < 2; ++hh) {
+          uint32_t sv[16], dv[16];
+          __syncwarp();
+          tmem_ld_32x32b_x16(tS + lane_off + qt * 32 + hh * 16, sv);
+          tmem_ld_32x32b_x16(tdP + lane_off + qt * 32 + hh * 16, dv);
+          tmem_ld_wait();
+          if (hh == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(s_free);   // S / dP are in registers: the next pair's may overwrite them
+          }
+          if (diag) {   // causal mask: only the diagonal tile pays for it (warp-uniform branch)
+#pragma unroll
+            for (int e = 0; e < 16; ++e)
+              if ((qt * 32 + hh * 16 + e) > r) sv[e] = 0xFF800000u;   // -inf -> probability 0 -> dS 0
+          }
+#pragma unroll
+          for (int g2 = 0; g2 < 2; ++g2) {
+            const int g = hh * 2 + g2;
+            uint4 rb = make_uint4(0u, 0u, 0u, 0u);   // thresh_hi is 0 without dropout: every lane kept
+            if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3));
+            const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
+            float pd[8], ds[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) {
+              const float qp = ex2_ftz(fmaf(__uint_as_float(sv[g2 * 8 + e]), kScale2, neg_lse));
+              const bool k1 = ((e & 1) ? w[e >> 1] : (w[e >> 1] << 16)) >= thresh_hi;
+              const float t = fmaf(__uint_as_float(dv[g2 * 8 + e]), kScale, neg_c);
+              ds[e] = qp * (k1 ? t : neg_c);
+              pd[e] = k1 ? qp : 0.f;
+            }
+            const int cc = (qt & 1) * 4 + g;
+            st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
+                         pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
+            st_shared_v4(swz(ds_sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
+                         pack_bf16x2(ds[4], ds[5]), pack_bf16x2(ds[6], ds[7]));
+          }
+        }
+        tc_fence_before();
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(&pds_ready[I & 1]);
+        if (it > 0) drain_dq(I - 1, it - 1);
+      }
+      drain_dq(I0 + niter - 1, niter - 1);
+
+      // dK / dV of this kv block: thread (r, qt) owns kv row r, head-dim columns [16 qt, 16 qt + 16)
+      mbar_wait(acc_full, ti & 1);
+      tc_fence_after();
+      const int kvrow = j * kBlk + r;
+      __nv_bfloat16* dk_dst = p.dqkv + size_t(row_base + kvrow) * 3 * h + h + hd * kD + qt * 16;
+      __nv_bfloat16* dv_dst = dk_dst + h;
+      {
+        uint32_t kv_[16], vv_[16];
+        __syncwarp();
+        tmem_ld_32x32b_x16(tdK + lane_off + qt * 16, kv_);
+        tmem_ld_32x32b_x16(tdV + lane_off + qt * 16, vv_);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(acc_free);   // accumulators are in registers: the next tile may start
+        if (kvrow < p.S) {
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            *reinterpret_cast<uint4*>(dk_dst + g * 8) = make_uint4(
+                pack_bf16x2(__uint_as_float(kv_[g * 8 + 0]), __uint_as_float(kv_[g * 8 + 1])),
+                pack_bf16x2(__uint_as_float(kv_[g * 8 + 2]), __uint_as_float(kv_[g * 8 + 3])),
+                pack_bf16x2(__uint_as_float(kv_[g * 8 + 4]), __uint_as_float(kv_[g * 8 + 5])),
+                pack_bf16x2(__uint_as_float(kv_[g * 8 + 6]), __uint_as_float(kv_[g * 8 + 7])));
+            *reinterpret_cast<uint4*>(dv_dst + g * 8) = make_uint4(
+                pack_bf16x2(__uint_as_float(vv_[g * 8 + 0]), __uint_as_float(vv_[g * 8 + 1])),
+                pack_bf16x2(__uint_as_float(vv_[g * 8 + 2]), __uint_as_float(vv_[g * 8 + 3])),
+                pack_bf16x2(__uint_as_float(vv_[g * 8 + 4]), __uint_as_float(vv_[g * 8 + 5])),
+                pack_bf16x2(__uint_as_float(vv_[g * 8 + 6]), __uint_as_float(vv_[g * 8 + 7])));
+          }
         }
       }
+      I0 += niter;
+      ++ti;
     }
   }
 
@@ -732,7 +783,8 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal));
     configured = true;
   }
-  dim3 grid(((seq + kBlk - 1) / kBlk) * heads * batch);
+  const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
+  dim3 grid(tiles < sm_count() ? tiles : sm_count());
   attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);
@@ -838,7 +890,8 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
-  dim3 grid(((seq + kBlk - 1) / kBlk) * heads * batch);
+  const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
+  dim3 grid(tiles < sm_count() ? tiles : sm_count());
   attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);
