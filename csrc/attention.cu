@@ -402,6 +402,81 @@ __global__ void attn_dq_cast_kernel(const float* __restrict__ dq, __nv_bfloat16*
       make_uint4(pack_bf16x2(a.x, a.y), pack_bf16x2(a.z, a.w), pack_bf16x2(bq.x, bq.y), pack_bf16x2(bq.z, bq.w));
 }
 
+// The two wrappers above plus the memset of the dQ accumulator and the rotary backward are four
+// memory-bound launches around the main kernel; the *_rope entry point runs them as two:
+//   attn_delta_zero_kernel : delta AND the zero-fill of dq_accum (eight lanes per (row, head), coalesced)
+//   attn_dq_rope_kernel    : dQ fp32 -> inverse rotary -> bf16 q columns, and the inverse rotary of the dK
+//                            columns in place (the rotation is applied to the fp32 dQ: one rounding, not two)
+__global__ void attn_delta_zero_kernel(const __nv_bfloat16* __restrict__ o, const __nv_bfloat16* __restrict__ d_o,
+                                       float* __restrict__ delta, float* __restrict__ dq, long long pairs, int S, int H) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  const long long rh = t >> 3;          // (row, head) pair; consecutive pairs are consecutive 64-column groups
+  const int sub = int(t & 7);
+  float acc = 0.f;
+  if (rh < pairs) {
+    const uint4 a = reinterpret_cast<const uint4*>(o + rh * kD)[sub], c = reinterpret_cast<const uint4*>(d_o + rh * kD)[sub];
+    const uint32_t aw[4] = {a.x, a.y, a.z, a.w}, cw[4] = {c.x, c.y, c.z, c.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(aw[e]), y = unpack_bf16x2(cw[e]);
+      acc += x.x * y.x + x.y * y.y;
+    }
+    float4* z = reinterpret_cast<float4*>(dq + rh * kD);
+    z[sub] = make_float4(0.f, 0.f, 0.f, 0.f);
+    z[sub + 8] = make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+#pragma unroll
+  for (int off = 4; off > 0; off >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, off);
+  if (rh < pairs && sub == 0) {
+    const long long row = rh / H;
+    const int hd = int(rh % H);
+    delta[((row / S) * H + hd) * S + (row % S)] = acc;
+  }
+}
+
+// thread per (row, which in {dQ, dK}, head, 8-wide group of the first half); pairs column j with j + 32
+__global__ void attn_dq_rope_kernel(const float* __restrict__ dq, __nv_bfloat16* __restrict__ dqkv,
+                                    const float* __restrict__ cs, const float* __restrict__ sn, long long total, int H,
+                                    int S) {
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= total) return;
+  const int g = int(t & 3);
+  const long long rh = t >> 2;
+  const int head2 = int(rh % (2 * H));   // 0..H-1: dQ heads, H..2H-1: dK heads
+  const long long row = rh / (2 * H);
+  const int pos = int(row % S), h = H * kD;
+  const float4* c4 = reinterpret_cast<const float4*>(cs + size_t(pos) * 32) + 2 * g;
+  const float4* s4 = reinterpret_cast<const float4*>(sn + size_t(pos) * 32) + 2 * g;
+  const float4 c0 = c4[0], c1 = c4[1], s0 = s4[0], s1 = s4[1];
+  const float cc[8] = {c0.x, c0.y, c0.z, c0.w, c1.x, c1.y, c1.z, c1.w};
+  const float ss[8] = {s0.x, s0.y, s0.z, s0.w, s1.x, s1.y, s1.z, s1.w};
+  __nv_bfloat16* dst = dqkv + row * 3 * h + head2 * kD + g * 8;   // dK columns start at h = H * 64
+  float a[8], b[8];
+  if (head2 < H) {
+    const float* src = dq + row * h + head2 * kD + g * 8;
+    const float4 a0 = *reinterpret_cast<const float4*>(src), a1 = *reinterpret_cast<const float4*>(src + 4);
+    const float4 b0 = *reinterpret_cast<const float4*>(src + 32), b1 = *reinterpret_cast<const float4*>(src + 36);
+    a[0] = a0.x; a[1] = a0.y; a[2] = a0.z; a[3] = a0.w; a[4] = a1.x; a[5] = a1.y; a[6] = a1.z; a[7] = a1.w;
+    b[0] = b0.x; b[1] = b0.y; b[2] = b0.z; b[3] = b0.w; b[4] = b1.x; b[5] = b1.y; b[6] = b1.z; b[7] = b1.w;
+  } else {
+    const uint4 lo = *reinterpret_cast<const uint4*>(dst), hi = *reinterpret_cast<const uint4*>(dst + 32);
+    const uint32_t low[4] = {lo.x, lo.y, lo.z, lo.w}, hiw[4] = {hi.x, hi.y, hi.z, hi.w};
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 x = unpack_bf16x2(low[e]), y = unpack_bf16x2(hiw[e]);
+      a[2 * e] = x.x; a[2 * e + 1] = x.y; b[2 * e] = y.x; b[2 * e + 1] = y.y;
+    }
+  }
+  uint32_t ol[4], oh[4];
+#pragma unroll
+  for (int e = 0; e < 4; ++e) {   // transpose of the forward rotation
+    ol[e] = pack_bf16x2(a[2 * e] * cc[2 * e] + b[2 * e] * ss[2 * e], a[2 * e + 1] * cc[2 * e + 1] + b[2 * e + 1] * ss[2 * e + 1]);
+    oh[e] = pack_bf16x2(b[2 * e] * cc[2 * e] - a[2 * e] * ss[2 * e], b[2 * e + 1] * cc[2 * e + 1] - a[2 * e + 1] * ss[2 * e + 1]);
+  }
+  *reinterpret_cast<uint4*>(dst) = make_uint4(ol[0], ol[1], ol[2], ol[3]);
+  *reinterpret_cast<uint4*>(dst + 32) = make_uint4(oh[0], oh[1], oh[2], oh[3]);
+}
+
 struct BwdSmem {
   static constexpr int kK = 0;
   static constexpr int kV = kK + kTile;
@@ -757,9 +832,28 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
   return 0;
 }
 
+static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta,
+                         float* dq_accum, int batch, int seq, int heads, float dropout_p, const unsigned long long* rng,
+                         unsigned int rng_stream, const float* rope_cos, const float* rope_sin, void* stream);
+
 int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta,
                   float* dq_accum, int batch, int seq, int heads, float dropout_p, const unsigned long long* rng,
                   unsigned int rng_stream, void* stream) {
+  return attn_bwd_impl(qkv, out, dout, lse, dqkv, delta, dq_accum, batch, seq, heads, dropout_p, rng, rng_stream, nullptr,
+                       nullptr, stream);
+}
+
+int b200_attn_bwd_rope(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta,
+                       float* dq_accum, int batch, int seq, int heads, float dropout_p, const unsigned long long* rng,
+                       unsigned int rng_stream, const float* rope_cos, const float* rope_sin, void* stream) {
+  B200_REQUIRE(rope_cos != nullptr && rope_sin != nullptr, "attn_bwd_rope: rotary tables required");
+  return attn_bwd_impl(qkv, out, dout, lse, dqkv, delta, dq_accum, batch, seq, heads, dropout_p, rng, rng_stream, rope_cos,
+                       rope_sin, stream);
+}
+
+static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, const float* lse, void* dqkv, float* delta,
+                         float* dq_accum, int batch, int seq, int heads, float dropout_p, const unsigned long long* rng,
+                         unsigned int rng_stream, const float* rope_cos, const float* rope_sin, void* stream) {
   B200_REQUIRE(batch > 0 && seq > 0 && heads > 0, "attn_bwd: empty problem");
   B200_REQUIRE(dropout_p == 0.f || rng != nullptr, "attn_bwd: rng_state required when dropout_p > 0");
   const int h = heads * kD;
@@ -771,10 +865,16 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
   if (rc) return rc;
   cudaStream_t s = STREAM(stream);
   const long long nd = rows * heads;
-  attn_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
-                                                                 delta, batch, seq, heads);
-  B200_CHECK_CUDA(cudaGetLastError());
-  B200_CHECK_CUDA(cudaMemsetAsync(dq_accum, 0, size_t(rows) * h * sizeof(float), s));
+  if (rope_cos != nullptr) {
+    attn_delta_zero_kernel<<<(unsigned)((nd * 8 + 255) / 256), 256, 0, s>>>(
+        (const __nv_bfloat16*)out, (const __nv_bfloat16*)dout, delta, dq_accum, nd, seq, heads);
+    B200_CHECK_CUDA(cudaGetLastError());
+  } else {
+    attn_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
+                                                                   delta, batch, seq, heads);
+    B200_CHECK_CUDA(cudaGetLastError());
+    B200_CHECK_CUDA(cudaMemsetAsync(dq_accum, 0, size_t(rows) * h * sizeof(float), s));
+  }
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
@@ -787,8 +887,14 @@ int b200_attn_bwd(const void* qkv, const void* out, const void* dout, const floa
   dim3 grid(tiles < sm_count() ? tiles : sm_count());
   attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
   B200_CHECK_CUDA(cudaGetLastError());
-  const long long ng = rows * (h / 8);
-  attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);
+  if (rope_cos != nullptr) {
+    const long long nt = rows * 2 * heads * 4;
+    attn_dq_rope_kernel<<<(unsigned)((nt + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rope_cos, rope_sin, nt,
+                                                                     heads, seq);
+  } else {
+    const long long ng = rows * (h / 8);
+    attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);
+  }
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -94,7 +94,11 @@ template <int NV>
 __global__ void __launch_bounds__(256, NV <= 3 ? 2 : 1)
 rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x,
                    const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd, float* __restrict__ dx,
-                   float* __restrict__ dw, int rows, int hidden) {
+                   float* __restrict__ dw, int rows, int hidden, __nv_bfloat16* __restrict__ dy_next, float p_next,
+                   const unsigned long long* __restrict__ rng, uint32_t rng_stream) {
+  // dy_next (optional): the updated dx, dropout-masked with stream `rng_stream` and cast to bf16 -- the
+  // dY of the residual branch that ends at this point of the stream (what dropout_bwd_cast would produce
+  // from dx in a second pass over it).
   extern __shared__ float s_dw[];  // [hidden]
   for (int i = threadIdx.x; i < hidden; i += blockDim.x) s_dw[i] = 0.f;
   __syncthreads();
@@ -163,6 +167,18 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict
         ob[k].w += r * d3.y * w3.y - xb[k].w * coef;
         dxr[2 * i] = oa[k];
         dxr[2 * i + 1] = ob[k];
+        if (dy_next != nullptr) {
+          float o[8] = {oa[k].x, oa[k].y, oa[k].z, oa[k].w, ob[k].x, ob[k].y, ob[k].z, ob[k].w};
+          if (p_next > 0.f) {
+            const float inv = 1.f / (1.f - p_next);
+#pragma unroll
+            for (int e = 0; e < 8; ++e) o[e] *= inv;
+            dropout_zero8(dropout_bits(rng[0], rng[1], rng_stream, (unsigned long long)row * nvec + i),
+                          dropout_threshold16(p_next) << 16, o);
+          }
+          reinterpret_cast<uint4*>(dy_next + size_t(row) * hidden)[i] =
+              make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+        }
       }
     }
   }
@@ -349,8 +365,16 @@ int b200_rmsnorm_fwd(const float* x, const void* w, void* y, float* rstd, int ro
 
 int b200_rmsnorm_bwd(const void* dy, const float* x, const void* w, const float* rstd, float* dx, float* dw, int rows,
                      int hidden, void* stream) {
+  return b200_rmsnorm_bwd_dropout(dy, x, w, rstd, dx, dw, rows, hidden, nullptr, 0.f, nullptr, 0, stream);
+}
+
+int b200_rmsnorm_bwd_dropout(const void* dy, const float* x, const void* w, const float* rstd, float* dx, float* dw,
+                             int rows, int hidden, void* dy_next_, float p_next, const unsigned long long* rng,
+                             unsigned int rng_stream, void* stream) {
   B200_REQUIRE(hidden % 8 == 0 && hidden <= kNormMaxVec * 256, "rmsnorm_bwd: hidden must be a multiple of 8 and <= %d",
                kNormMaxVec * 256);
+  B200_REQUIRE(dy_next_ == nullptr || p_next == 0.f || rng != nullptr, "rmsnorm_bwd: rng_state required when p > 0");
+  __nv_bfloat16* dy_next = (__nv_bfloat16*)dy_next_;
   int grid = sm_count() * 2;
   const int max_grid = (rows + 7) / 8;
   if (grid > max_grid) grid = max_grid;
@@ -358,7 +382,8 @@ int b200_rmsnorm_bwd(const void* dy, const float* x, const void* w, const float*
 #define B200_NORM_BWD(NV)                                                                         \
   case NV:                                                                                        \
     rmsnorm_bwd_kernel<NV><<<grid, 256, hidden * sizeof(float), STREAM(stream)>>>(                \
-        (const __nv_bfloat16*)dy, x, (const __nv_bfloat16*)w, rstd, dx, dw, rows, hidden);        \
+        (const __nv_bfloat16*)dy, x, (const __nv_bfloat16*)w, rstd, dx, dw, rows, hidden,         \
+        dy_next, p_next, rng, rng_stream);                                                        \
     break;
   switch (nv) {
     B200_NORM_BWD(1) B200_NORM_BWD(2) B200_NORM_BWD(3) B200_NORM_BWD(4)

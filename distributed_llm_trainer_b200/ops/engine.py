@@ -230,8 +230,8 @@ class FusedGPTEngine:
         h, I = cfg.hidden_size, cfg.intermediate_size
         rng = self.rng_state
         mc = self.max_ctas
-        # ---- MLP branch: x_out = xmid + dropout(down(act))
-        K.dropout_bwd_cast(ws.dx, ws.dy, cfg.dropout, rng, 8 * l + 2)
+        # ---- MLP branch: x_out = xmid + dropout(down(act)).  ws.dy = dropout'(ws.dx) for stream 8l+2 was
+        # written by the norm backward that produced ws.dx (fused dropout_bwd_cast).
         self._wgrad(ws.dy, a.act, G.wd)
         if self.fuse_swiglu_bwd:
             K.gemm(ws.dy, W.wd, ws.dgu, b_mn=True, epilogue=K.EPI_SWIGLU_BWD, aux=a.gu, half_n=I, N=I, max_ctas=mc)
@@ -241,17 +241,20 @@ class FusedGPTEngine:
             K.swiglu_bwd(ws.dact, a.gu, ws.dgu)
         self._wgrad(ws.dgu, a.xn2, G.wgu)
         K.gemm(ws.dgu, W.wgu, ws.dxn, b_mn=True, max_ctas=mc)
-        K.rmsnorm_bwd(ws.dxn, a.xmid, W.ln2, a.rstd2, ws.dx, G.ln2)
-        # ---- attention branch: xmid = x_in + dropout(o_proj(attn))
-        K.dropout_bwd_cast(ws.dx, ws.dy, cfg.dropout, rng, 8 * l + 1)
+        # ---- attention branch: xmid = x_in + dropout(o_proj(attn)); its dY comes out of the same pass
+        K.rmsnorm_bwd(ws.dxn, a.xmid, W.ln2, a.rstd2, ws.dx, G.ln2, dy_next=ws.dy, p_next=cfg.dropout, rng_state=rng,
+                      rng_stream=8 * l + 1)
         self._wgrad(ws.dy, a.attn, G.wo)
         K.gemm(ws.dy, W.wo, ws.dattn, b_mn=True, max_ctas=mc)
         K.attn_bwd(a.qkv, a.attn, ws.dattn, a.lse, ws.dqkv, ws.delta, ws.dq_acc, ws.B, ws.S, cfg.num_heads,
-                   cfg.attention_dropout, rng, 8 * l)
-        K.rope_inplace(ws.dqkv, self.rope_cos, self.rope_sin, 2 * h, ws.S, inverse=True)
+                   cfg.attention_dropout, rng, 8 * l, rope_cos=self.rope_cos, rope_sin=self.rope_sin)
         self._wgrad(ws.dqkv, a.xn1, G.wqkv)
         K.gemm(ws.dqkv, W.wqkv, ws.dxn, b_mn=True, max_ctas=mc)
-        K.rmsnorm_bwd(ws.dxn, x_in, W.ln1, a.rstd1, ws.dx, G.ln1)
+        if l > 0:   # ... and the dY of the previous block's MLP branch
+            K.rmsnorm_bwd(ws.dxn, x_in, W.ln1, a.rstd1, ws.dx, G.ln1, dy_next=ws.dy, p_next=cfg.dropout, rng_state=rng,
+                          rng_stream=8 * (l - 1) + 2)
+        else:
+            K.rmsnorm_bwd(ws.dxn, x_in, W.ln1, a.rstd1, ws.dx, G.ln1)
 
     # ------------------------------------------------------------------------------------------ LM head
     def _lm_head_loss(self, ws: _Workspace, loss_scale: float, with_grad: bool) -> None:
@@ -297,7 +300,8 @@ class FusedGPTEngine:
     def _backward_body(self, ws: _Workspace) -> None:
         L = self.cfg.num_layers
         ws.dx.zero_()
-        K.rmsnorm_bwd(ws.dxnf, ws.x[L], self.w_norm, ws.rstdf, ws.dx, self.g_norm)
+        K.rmsnorm_bwd(ws.dxnf, ws.x[L], self.w_norm, ws.rstdf, ws.dx, self.g_norm, dy_next=ws.dy,
+                      p_next=self.cfg.dropout, rng_state=self.rng_state, rng_stream=8 * (L - 1) + 2)
         for l in reversed(range(L)):
             if self.checkpointing:
                 self._layer_fwd(l, ws, ws.x[l], None, True, skip_last=True)

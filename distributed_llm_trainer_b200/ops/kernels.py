@@ -53,6 +53,7 @@ _SIGS = {
     "b200_embed_bwd": [_P, _P, _P, _I, _I, _I, _P],
     "b200_rmsnorm_fwd": [_P, _P, _P, _P, _I, _I, _F, _P],
     "b200_rmsnorm_bwd": [_P, _P, _P, _P, _P, _P, _I, _I, _P],
+    "b200_rmsnorm_bwd_dropout": [_P, _P, _P, _P, _P, _P, _I, _I, _P, _F, _P, _U, _P],
     "b200_resid_dropout_fwd": [_P, _P, _P, _I, _I, _F, _P, _U, _P],
     "b200_dropout_bwd_cast": [_P, _P, _I, _I, _F, _P, _U, _P],
     "b200_dropout_mask": [_P, _I, _I, _F, _P, _U, _P],
@@ -63,6 +64,7 @@ _SIGS = {
     "b200_attn_fwd": [_P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
     "b200_attn_fwd2": [_P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
     "b200_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
+    "b200_attn_bwd_rope": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _U, _P, _P, _P],
     "b200_ce_fwd_bwd": [_P, _P, _P, _I, _I, _I, _F, _F, _P],
     "b200_adamw": [_P, _P, _P, _P, _P, _P, _LL, _LL, _I, _F, _F, _F, _F, _F, _P, _P],
     "b200_sumsq": [_P, _LL, _LL, _P, _P],
@@ -168,10 +170,18 @@ def rmsnorm_fwd(x_f32, w_bf16, y_bf16, rstd, eps: float):
           eps, _stream())
 
 
-def rmsnorm_bwd(dy_bf16, x_f32, w_bf16, rstd, dx_accum, dw_accum):
+def rmsnorm_bwd(dy_bf16, x_f32, w_bf16, rstd, dx_accum, dw_accum, dy_next=None, p_next: float = 0.0, rng_state=None,
+                rng_stream: int = 0):
+    """``dx_accum += d/dx``, ``dw_accum += d/dw``; with ``dy_next`` also writes the dropout-masked bf16 copy of
+    the updated ``dx_accum`` (the following ``dropout_bwd_cast`` fused into this pass)."""
     rows, hidden = x_f32.shape
-    _call("b200_rmsnorm_bwd", dy_bf16.data_ptr(), x_f32.data_ptr(), w_bf16.data_ptr(), rstd.data_ptr(),
-          dx_accum.data_ptr(), dw_accum.data_ptr(), rows, hidden, _stream())
+    if dy_next is None:
+        _call("b200_rmsnorm_bwd", dy_bf16.data_ptr(), x_f32.data_ptr(), w_bf16.data_ptr(), rstd.data_ptr(),
+              dx_accum.data_ptr(), dw_accum.data_ptr(), rows, hidden, _stream())
+    else:
+        _call("b200_rmsnorm_bwd_dropout", dy_bf16.data_ptr(), x_f32.data_ptr(), w_bf16.data_ptr(), rstd.data_ptr(),
+              dx_accum.data_ptr(), dw_accum.data_ptr(), rows, hidden, dy_next.data_ptr(), p_next, _ptr(rng_state),
+              rng_stream, _stream())
 
 
 def resid_dropout_fwd(y_bf16, residual, out, p, rng_state, rng_stream):
@@ -220,10 +230,16 @@ def attn_fwd(qkv_bf16, out_bf16, lse, batch, seq, heads, dropout_p, rng_state, r
 
 
 def attn_bwd(qkv_bf16, out_bf16, dout_bf16, lse, dqkv_bf16, delta, dq_accum, batch, seq, heads, dropout_p, rng_state,
-             rng_stream):
-    _call("b200_attn_bwd", qkv_bf16.data_ptr(), out_bf16.data_ptr(), dout_bf16.data_ptr(), lse.data_ptr(),
-          dqkv_bf16.data_ptr(), delta.data_ptr(), dq_accum.data_ptr(), batch, seq, heads, dropout_p, _ptr(rng_state),
-          rng_stream, _stream())
+             rng_stream, rope_cos=None, rope_sin=None):
+    """With rotary tables the dQ / dK columns of ``dqkv`` come out rotated back (inverse RoPE fused in)."""
+    if rope_cos is None:
+        _call("b200_attn_bwd", qkv_bf16.data_ptr(), out_bf16.data_ptr(), dout_bf16.data_ptr(), lse.data_ptr(),
+              dqkv_bf16.data_ptr(), delta.data_ptr(), dq_accum.data_ptr(), batch, seq, heads, dropout_p, _ptr(rng_state),
+              rng_stream, _stream())
+    else:
+        _call("b200_attn_bwd_rope", qkv_bf16.data_ptr(), out_bf16.data_ptr(), dout_bf16.data_ptr(), lse.data_ptr(),
+              dqkv_bf16.data_ptr(), delta.data_ptr(), dq_accum.data_ptr(), batch, seq, heads, dropout_p, _ptr(rng_state),
+              rng_stream, rope_cos.data_ptr(), rope_sin.data_ptr(), _stream())
 
 
 # ----------------------------------------------------------------------------------------------- loss / optimizer

@@ -54,7 +54,7 @@ typedef struct b200_gemm_args {
   int a_mn_major, b_mn_major;
   int epilogue;   /* B200_EPI_* */
   int split_k;    /* <=1: none.  >1 requires B200_EPI_F32_ATOMIC */
-  int tile_n;     /* 128, 256, or 0 = choose by wave efficiency */
+  int tile_n;     /* 128, 256, 384 (pair kernel, N % 384 == 0, plain / residual epilogues), or 0 = choose by wave efficiency */
   int max_ctas;   /* 0 = all SMs; otherwise caps the persistent grid (leaves SMs for comm kernels) */
   /* rotary epilogue: fp32 tables [seq_len, 32] (head_dim 64, half-split pairing; reference gpt.py:116-147) */
   const float* rope_cos;
@@ -112,6 +112,12 @@ int b200_rmsnorm_fwd(const float* x, const void* w_bf16, void* y_bf16, float* rs
 /* dx (fp32) += d/dx ; dw (fp32 [hidden]) += d/dw (atomics).  dy is bf16. */
 int b200_rmsnorm_bwd(const void* dy_bf16, const float* x, const void* w_bf16, const float* rstd, float* dx_accum,
                      float* dw_accum, int rows, int hidden, void* stream);
+/* Same, and additionally dy_next(bf16) = dropout_mask(rng_stream) * dx_accum_updated / (1-p): the
+   b200_dropout_bwd_cast that follows a norm backward in the block's backward pass, without its second
+   pass over dx.  dy_next may be NULL (then identical to b200_rmsnorm_bwd). */
+int b200_rmsnorm_bwd_dropout(const void* dy_bf16, const float* x, const void* w_bf16, const float* rstd,
+                             float* dx_accum, float* dw_accum, int rows, int hidden, void* dy_next_bf16, float p,
+                             const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
 
 /* out(fp32) = residual + dropout(y bf16)   -- unfused companion of B200_EPI_RESID_DROPOUT */
 int b200_resid_dropout_fwd(const void* y_bf16, const float* residual, float* out, int rows, int cols, float p,
@@ -151,6 +157,13 @@ int b200_attn_fwd2(const void* qkv_bf16, void* out_bf16, float* lse, int batch, 
 int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
                   void* dqkv_bf16, float* delta, float* dq_accum, int batch, int seq, int heads, float dropout_p,
                   const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+/* Same, for q / k that went through the rotary embedding (B200_EPI_ROPE_BF16 in the QKV GEMM): the dQ and dK
+ * columns of dqkv come out already rotated back (b200_rope_inplace(..., inverse=1) folded into the final
+ * pass, the dQ rotation done in fp32 before the single rounding), and the delta / zero-fill passes are one. */
+int b200_attn_bwd_rope(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,
+                       void* dqkv_bf16, float* delta, float* dq_accum, int batch, int seq, int heads, float dropout_p,
+                       const unsigned long long* rng_state, unsigned int rng_stream, const float* rope_cos,
+                       const float* rope_sin, void* stream);
 
 /* Attention backward that allocates nothing and asks the caller for no scratch.  It has no counterpart in
  * the reference project; it exists for hosts that cannot hand this library device memory on demand (a

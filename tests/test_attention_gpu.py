@@ -59,3 +59,37 @@ def test_attention_fwd_bwd(B, S, H, p, impl):
         e = (g - r_).abs().max().item()
         scale = max(1.0, r_.abs().max().item())
         assert e < 0.04 * scale, f"{name} err {e} (scale {scale})"
+
+
+@pytest.mark.parametrize("B,S,H,p", [(2, 384, 3, 0.1), (1, 200, 2, 0.0)])
+def test_attention_bwd_with_fused_inverse_rope(B, S, H, p):
+    """b200_attn_bwd_rope == b200_attn_bwd followed by rope_inplace(inverse) on the dQ|dK columns."""
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    torch.manual_seed(1)
+    h = H * 64
+    qkv = (torch.randn(B * S, 3 * h, device="cuda") * 0.8).to(torch.bfloat16)
+    dout = (torch.randn(B * S, h, device="cuda") * 0.5).to(torch.bfloat16)
+    rng = torch.tensor([7, 1], dtype=torch.int64, device="cuda")
+    out = torch.zeros(B * S, h, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(B, H, S, device="cuda")
+    k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 2)
+    ang = torch.rand(S, 32, device="cuda") * 6.28
+    cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+    res = []
+    for fused in (False, True):
+        dqkv = torch.zeros(B * S, 3 * h, device="cuda", dtype=torch.bfloat16)
+        delta = torch.full((B, H, S), float("nan"), device="cuda")
+        dq_acc = torch.full((B * S, h), float("nan"), device="cuda")
+        if fused:
+            k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 2, rope_cos=cos, rope_sin=sin)
+        else:
+            k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 2)
+            k.rope_inplace(dqkv, cos, sin, 2 * h, S, inverse=True)
+        torch.cuda.synchronize()
+        res.append((dqkv.float(), delta.clone()))
+    assert torch.allclose(res[0][1], res[1][1], rtol=1e-5, atol=1e-5), "delta differs"
+    err = (res[0][0] - res[1][0]).abs().max().item()
+    scale = max(1.0, res[0][0].abs().max().item())
+    assert err < 0.02 * scale, f"fused inverse-rope differs: {err} (scale {scale})"
+    assert torch.equal(res[0][0][:, 2 * h:], res[1][0][:, 2 * h:]), "dV must be untouched by the rotary pass"

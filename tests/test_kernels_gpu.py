@@ -33,6 +33,18 @@ def test_rmsnorm_fwd_bwd(rows, hidden):
     torch.cuda.synchronize()
     assert (dx - 1 - xx.grad).abs().max().item() < 2e-3 * max(1.0, xx.grad.abs().max().item())
     assert (dw - ww.grad).abs().max().item() < 2e-3 * max(1.0, ww.grad.abs().max().item())
+    # fused variant: also emits dropout'(updated dx) in bf16, identical to the two-pass dropout_bwd_cast
+    rng = torch.tensor([11, 4], dtype=torch.int64, device="cuda")
+    for p in (0.0, 0.1):
+        dx2 = torch.ones(rows, hidden, device="cuda")
+        dw2 = torch.zeros(hidden, device="cuda")
+        dyn = torch.full((rows, hidden), float("nan"), device="cuda", dtype=torch.bfloat16)
+        k.rmsnorm_bwd(dy, x, w, rstd, dx2, dw2, dy_next=dyn, p_next=p, rng_state=rng, rng_stream=6)
+        two_pass = torch.empty_like(dyn)
+        k.dropout_bwd_cast(dx2, two_pass, p, rng, 6)
+        torch.cuda.synchronize()
+        assert torch.equal(dx2, dx) and torch.allclose(dw2, dw, rtol=1e-4, atol=1e-4)
+        assert torch.equal(dyn, two_pass), f"fused dropout-cast differs from dropout_bwd_cast at p={p}"
 
 
 def test_embedding_fwd_bwd():
