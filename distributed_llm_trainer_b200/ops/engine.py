@@ -297,11 +297,18 @@ class FusedGPTEngine:
                 self.release_hook(l, "forward")
         K.rmsnorm_fwd(ws.x[L], self.w_norm, ws.xnf, ws.rstdf, 1e-6)
 
-    def _backward_body(self, ws: _Workspace) -> None:
+    def _final_norm_bwd(self, ws: _Workspace) -> None:
+        """Start of the backward pass: ws.dx = d loss / d x[L] through the final norm, and ws.dy = its
+        dropout-masked bf16 copy for the last block's MLP branch (every _layer_bwd expects ws.dy on entry and
+        leaves the previous block's behind)."""
         L = self.cfg.num_layers
         ws.dx.zero_()
         K.rmsnorm_bwd(ws.dxnf, ws.x[L], self.w_norm, ws.rstdf, ws.dx, self.g_norm, dy_next=ws.dy,
                       p_next=self.cfg.dropout, rng_state=self.rng_state, rng_stream=8 * (L - 1) + 2)
+
+    def _backward_body(self, ws: _Workspace) -> None:
+        L = self.cfg.num_layers
+        self._final_norm_bwd(ws)
         for l in reversed(range(L)):
             if self.checkpointing:
                 self._layer_fwd(l, ws, ws.x[l], None, True, skip_last=True)

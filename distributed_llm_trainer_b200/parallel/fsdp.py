@@ -399,8 +399,7 @@ class ShardedGPT:
         e._lm_head_loss(ws, loss_scale, with_grad=True)
         # engine backward with per-block staging buffers
         L = self.L
-        ws.dx.zero_()
-        K.rmsnorm_bwd(ws.dxnf, ws.x[L], e.w_norm, ws.rstdf, ws.dx, e.g_norm)
+        e._final_norm_bwd(ws)
         for l in reversed(range(L)):
             slot, staging = self._stage_for(l)
             e.g_layers[l] = self._views(staging.local, l, self._LayerWeights)
