@@ -105,7 +105,13 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
-__device__ __forceinline__ float sigmoid_f(float x) { return __fdividef(1.0f, 1.0f + exp2f(-1.4426950408889634f * x)); }
+// two MUFU ops (EX2, RCP) and two FMA-pipe ops; exp2f() / __fdividef() add range checks the epilogue cannot afford
+__device__ __forceinline__ float sigmoid_f(float x) {
+  float e, r;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x));
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+  return r;
+}
 
 // tma_c: primary output.  tma_x: second tensor -- RESID_DROPOUT: residual (fp32, input); SWIGLU: act (bf16,
 // output); SWIGLU_BWD: saved [gate|up] (bf16, input).
@@ -516,21 +522,21 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           const int col0 = n0 + c * 32;
 #pragma unroll
           for (int g8 = 0; g8 < 2; ++g8) {
-            uint32_t keep = 0xFF;
-            if (drop) keep = dropout_keep8(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + hf * 2 + g8), thresh);
+            float a8[8];
+#pragma unroll
+            for (int e = 0; e < 8; ++e) a8[e] = __uint_as_float(v[g8 * 8 + e]) * inv_keep;
+            if (drop)   // compare + select per element straight off the Philox words (no bit-mask round trip)
+              dropout_zero8(dropout_bits(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + hf * 2 + g8)),
+                            thresh << 16, a8);
 #pragma unroll
             for (int hlf = 0; hlf < 2; ++hlf) {
               const int cl = g8 * 2 + hlf;                 // local 16-byte chunk (4 floats) of this thread's 16 columns
               const uint32_t addr = row_addr + (((hf * 4 + cl) ^ sw) << 4);
               const uint4 rq = ld_shared_v4(addr);
-              const float rr[4] = {__uint_as_float(rq.x), __uint_as_float(rq.y), __uint_as_float(rq.z), __uint_as_float(rq.w)};
-              uint32_t o[4];
-#pragma unroll
-              for (int e = 0; e < 4; ++e) {
-                const float a = ((keep >> (hlf * 4 + e)) & 1) ? __uint_as_float(v[cl * 4 + e]) * inv_keep : 0.f;
-                o[e] = __float_as_uint(rr[e] + a);
-              }
-              st_shared_v4_u32(addr, o[0], o[1], o[2], o[3]);
+              st_shared_v4_u32(addr, __float_as_uint(__uint_as_float(rq.x) + a8[hlf * 4 + 0]),
+                               __float_as_uint(__uint_as_float(rq.y) + a8[hlf * 4 + 1]),
+                               __float_as_uint(__uint_as_float(rq.z) + a8[hlf * 4 + 2]),
+                               __float_as_uint(__uint_as_float(rq.w) + a8[hlf * 4 + 3]));
             }
           }
           fence_proxy_async_smem();
@@ -602,8 +608,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
               const float2 gg = unpack_bf16x2(gw[e]), uu = unpack_bf16x2(uw[e]);
               const float da = __uint_as_float(d[cc * 8 + 2 * e]), db = __uint_as_float(d[cc * 8 + 2 * e + 1]);
               const float s0 = sigmoid_f(gg.x), s1 = sigmoid_f(gg.y);
-              og[e] = pack_bf16x2(da * uu.x * s0 * (1.0f + gg.x * (1.0f - s0)), db * uu.y * s1 * (1.0f + gg.y * (1.0f - s1)));
-              ou[e] = pack_bf16x2(da * gg.x * s0, db * gg.y * s1);
+              const float t0 = da * s0, t1 = db * s1;                       // d_act * sigmoid(gate)
+              // d silu(g)/dg = s (1 + g (1 - s));  1 + g (1 - s) = fma(g, 1 - s, 1)
+              og[e] = pack_bf16x2(t0 * uu.x * fmaf(gg.x, 1.0f - s0, 1.0f), t1 * uu.y * fmaf(gg.y, 1.0f - s1, 1.0f));
+              ou[e] = pack_bf16x2(t0 * gg.x, t1 * gg.y);
             }
             st_shared_v4_u32(g_row + off, og[0], og[1], og[2], og[3]);
             st_shared_v4_u32(u_row + off, ou[0], ou[1], ou[2], ou[3]);
