@@ -22,8 +22,15 @@ dq_acc = torch.empty(B * S, h, device="cuda")
 fwd = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=1)
 fwd2 = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=2)
 bwd = lambda: k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 9)
+ang = torch.rand(S, 32, device="cuda") * 6.28
+cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
+# what the engine runs: inverse RoPE of dQ|dK fused into the final pass; compare with bwd + rope_inplace
+bwd_rope = lambda: k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 9, rope_cos=cos, rope_sin=sin)
+bwd_then_rope = lambda: (bwd(), k.rope_inplace(dqkv, cos, sin, 2 * h, S, inverse=True))
 fwd(); bwd(); torch.cuda.synchronize()
 if os.environ.get("ATTN_TIME", "1") == "1":
     fl = 4.0 * B * H * S * S * 64 / 2
     tf, tb, tf2 = timeit(fwd), timeit(bwd), timeit(fwd2)
     print(f"p={p}: fwd {tf*1e3:.1f} us ({fl/tf/1e9:.0f} TFLOP/s causal)  fwd2 {tf2*1e3:.1f} us ({fl/tf2/1e9:.0f})  bwd {tb*1e3:.1f} us ({2.5*fl/tb/1e9:.0f} TFLOP/s)")
+    tr, tu = timeit(bwd_rope), timeit(bwd_then_rope)
+    print(f"p={p}: bwd + inverse RoPE fused {tr*1e3:.1f} us   unfused (bwd, then rope_inplace) {tu*1e3:.1f} us")
