@@ -14,6 +14,7 @@ and identical on all ranks, ``--config`` / ``--resume_from`` work.
 """
 from __future__ import annotations
 
+import contextlib
 import os
 import time
 from typing import Any, Dict, Optional
@@ -181,9 +182,14 @@ class FSDPTrainer:
         else:
             total = 0.0
             tsm = self.tsm
+            # reference fsdp_trainer.py:378: explicit autocast to the compute dtype (fp16 runs without a
+            # GradScaler there too, C26); CPU and fp32 run un-cast
+            amp = (torch.autocast("cuda", dtype=self.compute_dtype)
+                   if self.device.type == "cuda" and self.compute_dtype != torch.float32 else contextlib.nullcontext())
             for m in range(ga):
                 ids = input_ids[m * micro:(m + 1) * micro]
-                _, loss = self.model(ids, labels=ids.clone())
+                with amp:
+                    _, loss = self.model(ids, labels=ids.clone())
                 loss = loss / ga
                 loss.backward()
                 total += loss.item()
