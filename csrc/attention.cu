@@ -63,6 +63,32 @@ __device__ __forceinline__ float ex2_ftz(float x) {
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
 }
+// Packed fp32 pairs (FFMA2 / FADD2 / FMUL2 on sm_100): one issue slot for two lanes of the softmax math.
+__device__ __forceinline__ unsigned long long pk2(float lo, float hi) {
+  unsigned long long r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+  return r;
+}
+__device__ __forceinline__ float2 up2(unsigned long long v) {
+  float2 r;
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(r.x), "=f"(r.y) : "l"(v));
+  return r;
+}
+__device__ __forceinline__ float2 ffma2(float2 a, float2 b, float2 c) {
+  unsigned long long r;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y)), "l"(pk2(c.x, c.y)));
+  return up2(r);
+}
+__device__ __forceinline__ float2 fadd2(float2 a, float2 b) {
+  unsigned long long r;
+  asm("add.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y)));
+  return up2(r);
+}
+__device__ __forceinline__ float2 fmul2(float2 a, float2 b) {
+  unsigned long long r;
+  asm("mul.f32x2 %0, %1, %2;" : "=l"(r) : "l"(pk2(a.x, a.y)), "l"(pk2(b.x, b.y)));
+  return up2(r);
+}
 __device__ __forceinline__ void st_shared_v4(uint32_t addr, uint32_t a, uint32_t b, uint32_t c, uint32_t d) {
   asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(a), "r"(b), "r"(c), "r"(d) : "memory");
 }
@@ -267,7 +293,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         tmem_ld_32x32b_x16(tO[pb] + lane_off + qt * 16, v);
         tmem_ld_wait();
 #pragma unroll
-        for (int e = 0; e < 16; ++e) o[e] = o[e] * alpha + __uint_as_float(v[e]);
+        for (int e = 0; e < 16; e += 2) {   // FFMA2: two accumulator lanes per issue slot
+          const float2 t = ffma2(make_float2(o[e], o[e + 1]), make_float2(alpha, alpha),
+                                 make_float2(__uint_as_float(v[e]), __uint_as_float(v[e + 1])));
+          o[e] = t.x;
+          o[e + 1] = t.y;
+        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&o_free[pb]);
@@ -307,15 +338,18 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         const float neg_msc = -m_use * kScale2;
         // probabilities -> smem (bf16, dropout applied, unnormalised)
         const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + (qt >> 1) * kTile;
-        float l4[4] = {0.f, 0.f, 0.f, 0.f};
+        float2 l2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+        const float2 sc2 = make_float2(kScale2, kScale2), nm2 = make_float2(neg_msc, neg_msc);
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
           float pv[8];
 #pragma unroll
-          for (int e = 0; e < 8; ++e) {
-            // one FFMA + one MUFU per element; masked entries are ex2(-inf) = 0
-            pv[e] = ex2_ftz(fmaf(__uint_as_float(v[gq * 8 + e]), kScale2, neg_msc));
-            l4[e & 3] += pv[e];
+          for (int e = 0; e < 8; e += 2) {
+            // per PAIR of elements: one FFMA2 (exponent), two MUFU, one FADD2 (row sum); masked entries are ex2(-inf) = 0
+            const float2 arg = ffma2(make_float2(__uint_as_float(v[gq * 8 + e]), __uint_as_float(v[gq * 8 + e + 1])), sc2, nm2);
+            pv[e] = ex2_ftz(arg.x);
+            pv[e + 1] = ex2_ftz(arg.y);
+            l2[(e >> 1) & 1] = fadd2(l2[(e >> 1) & 1], make_float2(pv[e], pv[e + 1]));
           }
           if (drop)
             dropout_zero8(dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + gq * 8) >> 3)),
@@ -323,7 +357,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
           st_shared_v4(swz(sub, r, (qt & 1) * 4 + gq), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
                        pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
         }
-        l = l * alpha + ((l4[0] + l4[1]) + (l4[2] + l4[3]));
+        l = l * alpha + ((l2[0].x + l2[0].y) + (l2[1].x + l2[1].y));
         tc_fence_before();
         fence_proxy_async_smem();
         __syncwarp();
@@ -735,12 +769,18 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
             float pd[8], ds[8];
 #pragma unroll
-            for (int e = 0; e < 8; ++e) {
-              const float qp = ex2_ftz(fmaf(__uint_as_float(sv[g2 * 8 + e]), kScale2, neg_lse));
-              const bool k1 = ((e & 1) ? w[e >> 1] : (w[e >> 1] << 16)) >= thresh_hi;
-              const float t = fmaf(__uint_as_float(dv[g2 * 8 + e]), kScale, neg_c);
-              ds[e] = qp * (k1 ? t : neg_c);
-              pd[e] = k1 ? qp : 0.f;
+            for (int e = 0; e < 8; e += 2) {   // pairs: FFMA2 (exponent), FFMA2 (dP scale - c), FMUL2 (dS)
+              const float2 arg = ffma2(make_float2(__uint_as_float(sv[g2 * 8 + e]), __uint_as_float(sv[g2 * 8 + e + 1])),
+                                       make_float2(kScale2, kScale2), make_float2(neg_lse, neg_lse));
+              const float2 t = ffma2(make_float2(__uint_as_float(dv[g2 * 8 + e]), __uint_as_float(dv[g2 * 8 + e + 1])),
+                                     make_float2(kScale, kScale), make_float2(neg_c, neg_c));
+              const float qp0 = ex2_ftz(arg.x), qp1 = ex2_ftz(arg.y);
+              const bool k0 = (w[e >> 1] << 16) >= thresh_hi, k1 = w[e >> 1] >= thresh_hi;   // low / high 16-bit lane
+              const float2 d2 = fmul2(make_float2(qp0, qp1), make_float2(k0 ? t.x : neg_c, k1 ? t.y : neg_c));
+              ds[e] = d2.x;
+              ds[e + 1] = d2.y;
+              pd[e] = k0 ? qp0 : 0.f;
+              pd[e + 1] = k1 ? qp1 : 0.f;
             }
             const int cc = (qt & 1) * 4 + g;
             st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
