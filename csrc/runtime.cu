@@ -106,6 +106,15 @@ int b200_device_malloc(void** ptr, size_t bytes) {
   return 0;
 }
 
+// Stream-ordered copy between any two mapped device addresses (own or peer allocations): the copy
+// engines move it, no SM is involved -- the all-gathers of the sharded engine use this so that parameter
+// traffic never competes with the persistent GEMM / attention CTAs for SM resources.
+int b200_memcpy_async(void* dst, const void* src, size_t bytes, void* stream) {
+  if (bytes == 0) return 0;
+  B200_CHECK_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, reinterpret_cast<cudaStream_t>(stream)));
+  return 0;
+}
+
 int b200_device_free(void* ptr) {
   B200_CHECK_CUDA(cudaFree(ptr));
   return 0;

@@ -126,11 +126,12 @@ class FusedGPTEngine:
         self.rope_cos, self.rope_sin = rope_tables(cfg.max_seq_len, 64, device=self.device)
         self.rng_state = torch.tensor([seed & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=self.device)
         self._ws: Dict[Tuple[int, int, bool], _Workspace] = {}
-        self.use_graphs = True
+        self.use_graphs = __import__("os").environ.get("B200_NO_GRAPHS", "0") != "1"   # B200_NO_GRAPHS=1: eager launches (profiling)
         # epilogue-fusion switch (A/B-able): SwiGLU' inside the down-proj dgrad GEMM (CTA-pair kernel: gate|up
         # prefetched by TMA into the staging ring) vs GEMM + streaming kernel
         self.fuse_swiglu_bwd = True
         self.max_ctas = 0            # cap for GEMM grids when a comm kernel needs resident SMs
+        self.wgrad_overwrite = False  # True: every wgrad destination is written once per use (FSDP staging)
         self.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         # hooks used by the DDP / FSDP engines
         self.weights_hook: Optional[Callable[[int], LayerWeights]] = None   # FSDP: gathered weights for layer l
@@ -189,7 +190,15 @@ class FusedGPTEngine:
         bn = 256 if k_in % 256 == 0 else 128
         tiles = ((n_out + 127) // 128) * ((k_in + bn - 1) // bn)
         split = max(1, min(8, self.sm_count // max(tiles, 1)))
-        K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split, tile_n=bn,
+        epi = K.EPI_F32_ATOMIC
+        if self.wgrad_overwrite:
+            # the destination holds exactly one contribution (FSDP per-block staging): store instead of
+            # reduce-add, so the buffer needs no zero-fill; split-K still accumulates, over a zeroed matrix
+            if split > 1:
+                gw.zero_()
+            else:
+                epi = K.EPI_F32
+        K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=epi, split_k=split, tile_n=bn,
                max_ctas=self.max_ctas, M=n_out, N=k_in, K=dy.shape[0])
 
     def _weights(self, l: int) -> LayerWeights:

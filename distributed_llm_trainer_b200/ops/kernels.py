@@ -75,6 +75,7 @@ _SIGS = {
     "b200_adamw_bcast": [_P, _P, _P, _P, _P, _I, _I, _P, _LL, _LL, _I, _F, _F, _F, _F, _F, _P, _I, _P],
     "b200_allreduce_scalars": [_P, _I, _I, _P, _P, _P, _I, _P],
     "b200_all_gather_bf16": [_P, _P, _LL, _I, _I, _I, _P],
+    "b200_memcpy_async": [_P, _P, C.c_size_t, _P],
     "b200_all_gather_bf16_excl": [_P, _P, _LL, _I, _I, _LL, _LL, _I, _P],
     "b200_reduce_scatter_bf16_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
     "b200_reduce_scatter_f32_accum": [_P, _P, _LL, _LL, _F, _I, _I, _I, _P],
@@ -299,6 +300,13 @@ def adamw_bcast(master, grad, exp_avg, exp_avg_sq, shadow_ptrs, rank, world, dec
 def allreduce_scalars(pad_ptrs, rank, world, epoch_counter, inp, out, n):
     _call("b200_allreduce_scalars", pad_ptrs, rank, world, epoch_counter.data_ptr(), inp.data_ptr(), out.data_ptr(), n,
           _stream())
+
+
+def memcpy_async(dst_ptr: int, src_ptr: int, nbytes: int) -> None:
+    """Copy-engine transfer on the current stream between raw device addresses (peer mappings included)."""
+    rc = _fn("b200_memcpy_async")(dst_ptr, src_ptr, C.c_size_t(nbytes), _stream())   # not a kernel: not counted
+    if rc != 0:
+        _lib.check(rc, "b200_memcpy_async")
 
 
 def all_gather_bf16(shard_ptrs, dst, shard_elems, rank, world, max_ctas=0, exclude=(0, 0)):

@@ -157,7 +157,11 @@ class ShardedGPT:
         self.gather_pool = [torch.zeros(blk, dtype=torch.bfloat16, device=dev) for _ in range(max(n_gather, 1))]
         self.root_g = SymmetricBuffer(root, torch.float32, dev)
         self.grad_pool = [SymmetricBuffer(blk, torch.float32, dev) for _ in range(2)]
-        self.comm_stream = torch.cuda.Stream(device=dev)
+        self.comm_stream = torch.cuda.Stream(device=dev)     # gradient reductions (barrier / copy / sum / barrier)
+        # Parameter gathers get their own stream: queued behind a reduction they would wait for that reduction's
+        # barrier, i.e. for the slowest peer's backward, and stall the next block's weights_hook.
+        self.gather_stream = torch.cuda.Stream(device=dev)
+        self._params_ready: Optional[torch.cuda.Event] = None   # recorded after the optimizer step's barrier
         self.max_ctas = 0
         # all-gather fused into the QKV GEMM (B200_FSDP_FUSE_AG=0 gathers those rows with the rest of the unit)
         import os as _os
@@ -166,7 +170,15 @@ class ShardedGPT:
         h = model.config.hidden_size
         self.qkv_len = 3 * h * h
         self.qkv_off = (st.by_name["layers.0.attention.q_proj.weight"].offset - self.units[1].lo) if self.L > 0 else 0
-        self.fuse_ag = (_os.environ.get("B200_FSDP_FUSE_AG", "1") != "0" and self.L > 0
+        # Unit all-gathers ride the copy engines by default (B200_FSDP_CE_GATHER=0: the P2P-pull SM kernel).
+        self.ce_gather = _os.environ.get("B200_FSDP_CE_GATHER", "1") != "0"
+        # Same for the gradient reduce-scatter: copy-engine transfer + local sum (B200_FSDP_CE_RS=0: P2P-pull kernel)
+        self.ce_rs = _os.environ.get("B200_FSDP_CE_RS", "1") != "0"
+        self._rs_tmp: Dict[int, List[torch.Tensor]] = {}
+        # The fused all-gather GEMM is opt-in (B200_FSDP_FUSE_AG=1): a PREFETCHED gather hides completely under
+        # the previous block's compute, the fused one only under its own GEMM -- measured +7 ms / step on the
+        # 355M benchmark at 2 GPUs (profiles/fsdp_comm_breakdown.md).  It pays when nothing precedes the GEMM.
+        self.fuse_ag = (_os.environ.get("B200_FSDP_FUSE_AG", "0") != "0" and self.L > 0
                         and min(self.unit_part[1:]) >= 16384 and 3 * h >= 256)
         self.ag_pairs = int(_os.environ.get("B200_FSDP_AG_PAIRS", "2"))
         self._ag_flags = [torch.zeros((3 * h + 127) // 128, dtype=torch.int32, device=dev) for _ in self.gather_pool]
@@ -234,6 +246,7 @@ class ShardedGPT:
         e.end_step_hook = None
         e.hooks_capturable = False
         e.max_ctas = 0
+        e.wgrad_overwrite = True
         e.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self._LayerWeights = LayerWeights
         st = self.store
@@ -268,8 +281,24 @@ class ShardedGPT:
         from ..ops import kernels as K
 
         excl = (self.qkv_off, self.qkv_off + self.qkv_len) if skip_qkv else (0, 0)
-        K.all_gather_bf16(self._unit_ptrs(u), dst, self.unit_part[u], self.rank, self.world, self.max_ctas,
-                          exclude=excl)
+        if not self.ce_gather:
+            K.all_gather_bf16(self._unit_ptrs(u), dst, self.unit_part[u], self.rank, self.world, self.max_ctas,
+                              exclude=excl)
+            return
+        # Copy-engine all-gather: one stream-ordered P2P copy per (owner, segment).  No SM is used, so the
+        # gather overlaps the persistent GEMM / attention CTAs instead of sharing their SMs (measured:
+        # profiles/fsdp_comm_breakdown.md).
+        part = self.unit_part[u]
+        total = part * self.world
+        segs = [(0, total)] if excl[1] <= excl[0] else [(0, excl[0]), (excl[1], total)]
+        base = dst.data_ptr()
+        src_off = self.shard_off[u]
+        for r in range(self.world):
+            lo, hi = r * part, (r + 1) * part
+            for a, b in segs:
+                a2, b2 = max(a, lo), min(b, hi)
+                if b2 > a2:
+                    K.memcpy_async(base + 2 * a2, self.shard_bf16.raw_ptrs[r] + 2 * (src_off + a2 - lo), 2 * (b2 - a2))
 
     def _fuse_qkv_now(self) -> bool:
         """Will the QKV GEMM run on the weights gathered in the current phase?  Forward: always.  Backward:
@@ -300,9 +329,11 @@ class ShardedGPT:
         if all(o is not None for o in self._slot_owner):
             return
         slot = self._acquire_slot(l)
-        cs = self.comm_stream
+        cs = self.gather_stream
         if self._slot_free_evt[slot] is not None:
             cs.wait_event(self._slot_free_evt[slot])
+        if self._params_ready is not None:
+            cs.wait_event(self._params_ready)       # never read a peer's shard while its AdamW may be writing it
         fused = self._fuse_qkv_now()
         with torch.cuda.stream(cs):
             self._gather_unit(1 + l, self.gather_pool[slot], skip_qkv=fused)
@@ -333,9 +364,9 @@ class ShardedGPT:
         ev = self._gslot_free_evt[slot]
         if ev is not None:
             torch.cuda.current_stream().wait_event(ev)
-        buf = self.grad_pool[slot]
-        buf.local.zero_()
-        return slot, buf
+        # no zero-fill: wgrad GEMMs overwrite (engine.wgrad_overwrite), the two norm gradients are cleared by
+        # the caller, and the alignment padding between parameters is never written after allocation
+        return slot, self.grad_pool[slot]
 
     def _reduce_unit(self, u: int, staging) -> torch.cuda.Event:
         """comm stream: barrier (all ranks produced unit u) -> reduce own slice -> barrier (all done reading)."""
@@ -353,7 +384,25 @@ class ShardedGPT:
             n = min(part, max(0, (self.units[u].hi - self.units[u].lo) - lo))
             n = (n + 3) // 4 * 4
             dst = self.grad_shard[self.shard_off[u]: self.shard_off[u] + part]
-            if n > 0:
+            if n > 0 and self.ce_rs and self.world > 1:
+                # Copy engines bring the peers' copies of this rank's slice next to the local one; the sum is
+                # then a local streaming kernel.  The SMs never stall on NVLink loads and the transfer does not
+                # occupy the SMs the persistent GEMM / attention CTAs are using.
+                tmps = self._rs_tmp.get(id(staging))
+                if tmps is None:
+                    tmps = [torch.empty(part, dtype=torch.float32, device=self.device) for _ in range(self.world - 1)]
+                    self._rs_tmp[id(staging)] = tmps
+                tab, k = [], 0
+                for r in range(self.world):
+                    if r == self.rank:
+                        tab.append(staging.raw_ptrs[r])
+                    else:
+                        K.memcpy_async(tmps[k].data_ptr(), staging.raw_ptrs[r] + 4 * lo, 4 * n)
+                        tab.append(tmps[k].data_ptr() - 4 * lo)     # the kernel indexes every source at `lo`
+                        k += 1
+                K.reduce_scatter_f32_accum(K.ptr_array(tab), dst, lo, n, 1.0 / self.world, self.rank, self.world,
+                                           self.max_ctas)
+            elif n > 0:
                 K.reduce_scatter_f32_accum(staging.ptrs, dst, lo, n, 1.0 / self.world, self.rank, self.world,
                                            self.max_ctas)
             self.pads.barrier()
@@ -402,7 +451,10 @@ class ShardedGPT:
         e._final_norm_bwd(ws)
         for l in reversed(range(L)):
             slot, staging = self._stage_for(l)
-            e.g_layers[l] = self._views(staging.local, l, self._LayerWeights)
+            g = self._views(staging.local, l, self._LayerWeights)
+            g.ln1.zero_()           # RMSNorm weight gradients accumulate with atomics
+            g.ln2.zero_()
+            e.g_layers[l] = g
             if e.checkpointing:
                 e._layer_fwd(l, ws, ws.x[l], None, True, skip_last=True)
             e._layer_bwd(l, ws, ws.x[l])
@@ -421,6 +473,7 @@ class ShardedGPT:
 
         cur = torch.cuda.current_stream()
         cur.wait_stream(self.comm_stream)
+        cur.wait_stream(self.gather_stream)         # no gather may still be reading the shards AdamW rewrites
         self.sumsq.zero_()
         K.sumsq(self.grad_shard, 0, self.shard_total, self.sumsq[0:1])
         self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
@@ -432,6 +485,8 @@ class ShardedGPT:
             self._step_offloaded(opt_state, lr, b1, b2, eps, wd)
             self.grad_shard.zero_()
             self.pads.barrier()
+            self._params_ready = torch.cuda.Event()
+            self._params_ready.record(cur)
             self._root_done = None
             self._root_stale = True
             return
@@ -447,6 +502,8 @@ class ShardedGPT:
         self.grad_shard.zero_()
         # peers may gather my new slices only after every rank finished its update
         self.pads.barrier()
+        self._params_ready = torch.cuda.Event()
+        self._params_ready.record(cur)
         self._root_done = None
         self._root_stale = True
 

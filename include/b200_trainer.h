@@ -33,6 +33,8 @@ int b200_ipc_export(void* ptr, void* handle64 /* host, 64 bytes out */);
 int b200_ipc_open(const void* handle64 /* host */, void** ptr);
 int b200_ipc_close(void* ptr);
 int b200_enable_peer_access(int peer_device);
+/* Stream-ordered copy-engine transfer between mapped device addresses (local or peer). */
+int b200_memcpy_async(void* dst, const void* src, size_t bytes, void* stream);
 
 /* ---------------------------------------------------------------- GEMM (tcgen05 / TMEM / TMA) */
 enum {

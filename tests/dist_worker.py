@@ -305,7 +305,12 @@ def main():
         mode_ddp(tmp)
     elif mode.startswith("fsdp"):
         parts = mode.split(":")
-        mode_fsdp(tmp, parts[1], offload=len(parts) > 2 and parts[2] == "offload")
+        opt = parts[2] if len(parts) > 2 else ""
+        if opt == "fuseag":       # QKV rows gathered inside the QKV GEMM (b200_gemm2_ag_bf16), rest prefetched
+            os.environ["B200_FSDP_FUSE_AG"] = "1"
+        if opt == "smgather":     # P2P-pull SM kernel instead of copy-engine gathers
+            os.environ["B200_FSDP_CE_GATHER"] = "0"
+        mode_fsdp(tmp, parts[1], offload=opt == "offload")
     elif mode == "comm":
         mode_comm(tmp)
     elif mode == "aggemm":
