@@ -156,7 +156,19 @@ class ShardedGPT:
         self.root_w = torch.zeros(root + slack, dtype=torch.bfloat16, device=dev)
         self.gather_pool = [torch.zeros(blk, dtype=torch.bfloat16, device=dev) for _ in range(max(n_gather, 1))]
         self.root_g = SymmetricBuffer(root, torch.float32, dev)
-        self.grad_pool = [SymmetricBuffer(blk, torch.float32, dev) for _ in range(2)]
+        # Gradient accumulation across micro-steps.  accum_local (default when it fits): every block unit has its own
+        # peer-mapped fp32 buffer that accumulates over the micro-steps of a step and is reduce-scattered ONCE, on
+        # the last one -- 180 GB of HBM makes the reference's "reduce-scatter every micro-step" (FSDP1 without
+        # no_sync, fsdp_trainer.py:369-384) an avoidable cost: GA x less traffic and GA x fewer barriers.
+        # B200_FSDP_ACCUM_LOCAL=0 restores the per-micro-step reduction through two rotating staging buffers
+        # (gradient memory / world, the reference's footprint).
+        import os as _os0
+        full_bytes = 4 * blk * self.L
+        free_b, _tot = torch.cuda.mem_get_info(dev)
+        self.accum_local = (_os0.environ.get("B200_FSDP_ACCUM_LOCAL", "1") != "0" and self.L > 0
+                            and full_bytes < 0.25 * free_b)
+        n_stage = self.L if self.accum_local else 2
+        self.grad_pool = [SymmetricBuffer(blk, torch.float32, dev) for _ in range(n_stage)]
         self.comm_stream = torch.cuda.Stream(device=dev)     # gradient reductions (barrier / copy / sum / barrier)
         # Parameter gathers get their own stream: queued behind a reduction they would wait for that reduction's
         # barrier, i.e. for the slowest peer's backward, and stall the next block's weights_hook.
@@ -191,7 +203,7 @@ class ShardedGPT:
         self._gathered: Dict[int, Tuple[int, torch.cuda.Event]] = {}   # layer -> (pool slot, ready event)
         self._slot_free_evt: List[Optional[torch.cuda.Event]] = [None] * len(self.gather_pool)
         self._slot_owner: List[Optional[int]] = [None] * len(self.gather_pool)
-        self._gslot_free_evt: List[Optional[torch.cuda.Event]] = [None, None]
+        self._gslot_free_evt: List[Optional[torch.cuda.Event]] = [None] * len(self.grad_pool)
         self._root_ready: Optional[torch.cuda.Event] = None
         self._phase = "idle"
         torch.cuda.synchronize()
@@ -246,7 +258,7 @@ class ShardedGPT:
         e.end_step_hook = None
         e.hooks_capturable = False
         e.max_ctas = 0
-        e.wgrad_overwrite = True
+        e.wgrad_overwrite = not self.accum_local    # rotating staging buffers hold one contribution per use
         e.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self._LayerWeights = LayerWeights
         st = self.store
@@ -360,7 +372,7 @@ class ShardedGPT:
 
     # ------------------------------------------------------------------------------------------ grad staging
     def _stage_for(self, l: int):
-        slot = l & 1
+        slot = l if self.accum_local else (l & 1)
         ev = self._gslot_free_evt[slot]
         if ev is not None:
             torch.cuda.current_stream().wait_event(ev)
@@ -388,10 +400,10 @@ class ShardedGPT:
                 # Copy engines bring the peers' copies of this rank's slice next to the local one; the sum is
                 # then a local streaming kernel.  The SMs never stall on NVLink loads and the transfer does not
                 # occupy the SMs the persistent GEMM / attention CTAs are using.
-                tmps = self._rs_tmp.get(id(staging))
+                tmps = self._rs_tmp.get(part)      # shared by all units of this size: reductions are stream-ordered
                 if tmps is None:
                     tmps = [torch.empty(part, dtype=torch.float32, device=self.device) for _ in range(self.world - 1)]
-                    self._rs_tmp[id(staging)] = tmps
+                    self._rs_tmp[part] = tmps
                 tab, k = [], 0
                 for r in range(self.world):
                     if r == self.rank:
@@ -406,6 +418,8 @@ class ShardedGPT:
                 K.reduce_scatter_f32_accum(staging.ptrs, dst, lo, n, 1.0 / self.world, self.rank, self.world,
                                            self.max_ctas)
             self.pads.barrier()
+            if self.accum_local:
+                staging.local.zero_()      # every peer has read its slice: start the next step's accumulation at 0
             done.record(cs)
         return done
 
@@ -415,18 +429,26 @@ class ShardedGPT:
                 self._free_gathered(l)
             return
         # backward of block l finished: its staging buffer holds this rank's full-unit gradient
-        slot = l & 1
-        self._gslot_free_evt[slot] = self._reduce_unit(1 + l, self.grad_pool[slot])
+        if self.accum_local:
+            if self._last_micro:
+                self._gslot_free_evt[l] = self._reduce_unit(1 + l, self.grad_pool[l])
+        else:
+            slot = l & 1
+            self._gslot_free_evt[slot] = self._reduce_unit(1 + l, self.grad_pool[slot])
         self._free_gathered(l)
 
     def _grad_ready_hook(self, unit: int) -> None:
-        if unit == 0:
+        if unit == 0 and (self._last_micro or not self.accum_local):
             self._root_done = self._reduce_unit(0, self.root_g)
 
     # ------------------------------------------------------------------------------------------ micro-step
-    def forward_backward(self, input_ids: torch.Tensor, labels: torch.Tensor, loss_scale: float) -> torch.Tensor:
+    def forward_backward(self, input_ids: torch.Tensor, labels: torch.Tensor, loss_scale: float,
+                         last: bool = True) -> torch.Tensor:
+        """One micro-step.  ``last``: this is the final micro-step before ``step()`` -- with local accumulation the
+        gradient reduce-scatter only happens then (callers that never pass it reduce every micro-step)."""
         from ..ops import kernels as K
 
+        self._last_micro = bool(last)
         e = self.engine
         B, S = input_ids.shape
         ws = e.workspace(B, S, True)
@@ -438,7 +460,8 @@ class ShardedGPT:
         if getattr(self, "_root_stale", True):
             self._gather_unit(0, self.root_w)       # parameters only change at the optimizer step
             self._root_stale = False
-        self.root_g.local.zero_()
+        if not self.accum_local:
+            self.root_g.local.zero_()               # accum_local: zeroed on the comm stream after each reduction
         ws.loss_sum.zero_()
         self._phase = "forward"
         self._prefetch(0)
@@ -452,8 +475,9 @@ class ShardedGPT:
         for l in reversed(range(L)):
             slot, staging = self._stage_for(l)
             g = self._views(staging.local, l, self._LayerWeights)
-            g.ln1.zero_()           # RMSNorm weight gradients accumulate with atomics
-            g.ln2.zero_()
+            if not self.accum_local:
+                g.ln1.zero_()       # RMSNorm weight gradients accumulate with atomics
+                g.ln2.zero_()
             e.g_layers[l] = g
             if e.checkpointing:
                 e._layer_fwd(l, ws, ws.x[l], None, True, skip_last=True)

@@ -161,7 +161,10 @@ class FSDPTrainer:
             runner = self.sharded if self.sharded is not None else self.engine
             for m in range(ga):
                 ids = input_ids[m * micro:(m + 1) * micro]
-                self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga))
+                if self.sharded is not None:
+                    self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga, last=(m == ga - 1)))
+                else:
+                    self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga))
             g0 = self.optimizer.param_groups[0]
             if self.sharded is not None:
                 self.sharded.step(self.opt_state, g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"], cfg.grad_clip,

@@ -308,8 +308,11 @@ def main():
         opt = parts[2] if len(parts) > 2 else ""
         if opt == "fuseag":       # QKV rows gathered inside the QKV GEMM (b200_gemm2_ag_bf16), rest prefetched
             os.environ["B200_FSDP_FUSE_AG"] = "1"
-        if opt == "smgather":     # P2P-pull SM kernel instead of copy-engine gathers
+        if opt == "smgather":     # P2P-pull SM kernels instead of copy-engine gathers / reduce-scatter transfers
             os.environ["B200_FSDP_CE_GATHER"] = "0"
+            os.environ["B200_FSDP_CE_RS"] = "0"
+        if opt == "everymicro":   # reduce-scatter every micro-step through the two rotating staging buffers
+            os.environ["B200_FSDP_ACCUM_LOCAL"] = "0"
         mode_fsdp(tmp, parts[1], offload=opt == "offload")
     elif mode == "comm":
         mode_comm(tmp)
