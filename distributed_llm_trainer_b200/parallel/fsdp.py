@@ -8,12 +8,15 @@ NO_SHARD (:269-274), bf16 parameters + communication with fp32 sharded master we
 
 ``ShardedGPT`` (CUDA / bf16 engine path)
     * every rank keeps only its 1/N slice of each unit in bf16 (peer-mapped) + fp32 optimizer state;
-    * forward/backward walk the units: ``b200_all_gather_bf16`` pulls the peers' slices over NVLink
-      into a pooled unit buffer on a side stream (next unit prefetched while the current one computes;
-      FULL_SHARD frees it after use and gathers again in backward, SHARD_GRAD_OP keeps it);
-    * wgrad GEMMs accumulate fp32 gradients into a peer-mapped unit staging buffer;
-      ``b200_reduce_scatter_f32`` (accumulate mode) then sums *this rank's slice* from all peers into
-      the sharded fp32 gradient -- every micro-step, as FSDP does (the reference has no ``no_sync``);
+    * forward/backward walk the units: the peers' slices are copied over NVLink (copy engines,
+      ``b200_memcpy_async``; optionally the ``b200_all_gather_bf16`` pull kernel) into a pooled unit
+      buffer on a gather stream (next unit prefetched while the current one computes; FULL_SHARD
+      frees it after use and gathers again in backward, SHARD_GRAD_OP keeps it);
+    * wgrad GEMMs write fp32 gradients into peer-mapped per-block buffers that accumulate over the
+      micro-steps of a step; on the last micro-step each rank copies the peers' versions of *its*
+      slice over and sums them into the sharded fp32 gradient (``b200_reduce_scatter_f32_accum``).
+      ``B200_FSDP_ACCUM_LOCAL=0`` reduces every micro-step through two rotating staging buffers
+      instead, as FSDP1 does (the reference has no ``no_sync``);
     * the step is: sharded norm^2 -> pad all-reduce -> clip coefficient -> fused AdamW on the shard,
       writing the bf16 slice peers will gather next step.
 
