@@ -190,6 +190,10 @@ class ShardedGPT:
         # Same for the gradient reduce-scatter: copy-engine transfer + local sum (B200_FSDP_CE_RS=0: P2P-pull kernel)
         self.ce_rs = _os.environ.get("B200_FSDP_CE_RS", "1") != "0"
         self._rs_tmp: Dict[int, List[torch.Tensor]] = {}
+        self.use_graphs = (_os.environ.get("B200_FSDP_GRAPHS", "1") != "0"
+                           and _os.environ.get("B200_NO_GRAPHS", "0") != "1")
+        self._graphs: Dict[Tuple[int, int, float], Any] = {}
+        self._plain_calls = 0
         # The fused all-gather GEMM is opt-in (B200_FSDP_FUSE_AG=1): a PREFETCHED gather hides completely under
         # the previous block's compute, the fused one only under its own GEMM -- measured +7 ms / step on the
         # 355M benchmark at 2 GPUs (profiles/fsdp_comm_breakdown.md).  It pays when nothing precedes the GEMM.
@@ -448,7 +452,11 @@ class ShardedGPT:
     def forward_backward(self, input_ids: torch.Tensor, labels: torch.Tensor, loss_scale: float,
                          last: bool = True) -> torch.Tensor:
         """One micro-step.  ``last``: this is the final micro-step before ``step()`` -- with local accumulation the
-        gradient reduce-scatter only happens then (callers that never pass it reduce every micro-step)."""
+        gradient reduce-scatter only happens then (callers that never pass it reduce every micro-step).
+
+        Micro-steps without a reduction are pure compute + copy-engine gathers with a fixed host-side schedule
+        (pool slots, events), so from the third one on they are replayed from a CUDA graph that spans the main
+        and the gather stream (B200_FSDP_GRAPHS=0 / B200_NO_GRAPHS=1: always eager)."""
         from ..ops import kernels as K
 
         self._last_micro = bool(last)
@@ -460,11 +468,53 @@ class ShardedGPT:
         # root unit: gathered once per micro-step, stays resident (as FSDP's root does)
         if getattr(self, "_root_done", None) is not None:
             cur.wait_event(self._root_done)
+            self._root_done = None
         if getattr(self, "_root_stale", True):
             self._gather_unit(0, self.root_w)       # parameters only change at the optimizer step
             self._root_stale = False
         if not self.accum_local:
             self.root_g.local.zero_()               # accum_local: zeroed on the comm stream after each reduction
+        if not (self.use_graphs and self.accum_local and not last and not self.fuse_ag):
+            self._micro_body(ws, loss_scale)
+            return ws.loss_sum
+        key = (B, S, float(loss_scale))
+        entry = self._graphs.get(key)
+        self._plain_calls += 1
+        if entry is None and self._plain_calls > 2:
+            # every dependency inside the capture must be on captured work: join the side streams and drop the
+            # events of earlier (eager) micro-steps -- stream order of the graph launch covers them
+            cur.wait_stream(self.gather_stream)
+            cur.wait_stream(self.comm_stream)
+            torch.cuda.synchronize()
+            self._drop_events()
+            g = torch.cuda.CUDAGraph()
+            before = K.launch_count
+            with torch.cuda.graph(g):
+                self._micro_body(ws, loss_scale)
+                torch.cuda.current_stream().wait_stream(self.gather_stream)     # join the forked stream
+            self._drop_events()                     # events recorded during capture mean nothing outside it
+            entry = (g, K.launch_count - before)
+            K.launch_count = before
+            self._graphs[key] = entry
+        if entry is None:
+            self._micro_body(ws, loss_scale)
+        else:
+            entry[0].replay()
+            K.launch_count += entry[1]
+        return ws.loss_sum
+
+    def _drop_events(self) -> None:
+        self._slot_free_evt = [None] * len(self.gather_pool)
+        self._gslot_free_evt = [None] * len(self.grad_pool)
+        self._params_ready = None
+
+    def _micro_body(self, ws, loss_scale: float) -> None:
+        from ..ops import kernels as K
+
+        e = self.engine
+        # fork: gathers issued from here on are ordered after everything already on the main stream (and, under
+        # capture, this is what pulls the gather stream into the graph)
+        self.gather_stream.wait_stream(torch.cuda.current_stream())
         ws.loss_sum.zero_()
         self._phase = "forward"
         self._prefetch(0)
@@ -490,7 +540,6 @@ class ShardedGPT:
         self._grad_ready_hook(0)
         K.rng_advance(e.rng_state, 1)
         self._phase = "idle"
-        return ws.loss_sum
 
     # ------------------------------------------------------------------------------------------ optimizer step
     def step(self, opt_state, lr: float, betas, eps: float, wd: float, grad_clip: float,
