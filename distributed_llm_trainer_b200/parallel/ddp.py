@@ -127,9 +127,38 @@ class NVLinkGradSync:
         self.overlap = __import__("os").environ.get("B200_DDP_OVERLAP", "0") == "1"
         # small grid: shares the SMs with the backward GEMMs it overlaps
         self.comm_ctas = int(__import__("os").environ.get("B200_DDP_COMM_CTAS", "32"))
+        # B200_DDP_CE=1: peers' copies of the owned slice come over by copy engine into local scratch and the
+        # reduction kernel reads local memory only (no SM time spent waiting on NVLink loads)
+        self.ce = __import__("os").environ.get("B200_DDP_CE", "0") == "1"
+        self._ce_tmp: Optional[List[torch.Tensor]] = None
         self._last = False
         self._overlapped = False
         self._units_done = 0
+
+    def _reduce_range(self, lo: int, hi: int, ctas: int) -> None:
+        """store.grad[lo:hi] = mean over ranks of their grad[lo:hi]; adds the slice's squared norm to sumsq[0]."""
+        from ..ops import kernels as K
+
+        if hi <= lo:
+            return
+        ptrs = self.grad_buf.ptrs
+        if self.ce and self.world > 1:
+            if self._ce_tmp is None:
+                mx = max(b - a for a, b in self.ranges)
+                self._ce_tmp = [torch.empty(mx, dtype=torch.float32, device=self.store.device)
+                                for _ in range(self.world - 1)]
+            tab, k = [], 0
+            for r in range(self.world):
+                if r == self.rank:
+                    tab.append(self.grad_buf.raw_ptrs[r])
+                else:
+                    t = self._ce_tmp[k]
+                    k += 1
+                    K.memcpy_async(t.data_ptr(), self.grad_buf.raw_ptrs[r] + 4 * lo, 4 * (hi - lo))
+                    tab.append(t.data_ptr() - 4 * lo)          # the kernel indexes every source at [lo, hi)
+            ptrs = K.ptr_array(tab)
+        K.reduce_scatter_f32(ptrs, self.store.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1], self.rank, self.world,
+                             ctas)
 
     def owned_ranges(self) -> List[Tuple[int, int]]:
         return self.ranges
@@ -162,8 +191,7 @@ class NVLinkGradSync:
         lo, hi = self.ranges[unit]
         with torch.cuda.stream(self.comm_stream):
             self.pads.barrier()      # every rank has finished this unit's gradients
-            K.reduce_scatter_f32(self.grad_buf.ptrs, self.store.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1],
-                                 self.rank, self.world, self.comm_ctas)
+            self._reduce_range(lo, hi, self.comm_ctas)
         self._units_done += 1
 
     def _join_comm(self) -> None:
@@ -188,8 +216,7 @@ class NVLinkGradSync:
             # every rank's backward has finished writing its gradients
             self.pads.barrier()
             for lo, hi in self.ranges:
-                K.reduce_scatter_f32(self.grad_buf.ptrs, st.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1], self.rank,
-                                     self.world, self.max_ctas)
+                self._reduce_range(lo, hi, self.max_ctas)
         # global gradient norm: sum of the per-rank partials (identical summation order everywhere)
         self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
         K.clip_coef(self.sumsq_total, float(grad_clip), 1.0, opt.grad_scale, norm_out)

@@ -299,9 +299,11 @@ def main():
     tmp = sys.argv[2] if len(sys.argv) > 2 else "/tmp/b200_dist_test"
     os.makedirs(tmp, exist_ok=True)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    if mode in ("ddp", "ddp:overlap"):
-        if mode == "ddp:overlap":
+    if mode in ("ddp", "ddp:overlap", "ddp:ce", "ddp:overlapce"):
+        if "overlap" in mode:
             os.environ["B200_DDP_OVERLAP"] = "1"    # fork the per-unit reductions under the last backward
+        if mode.endswith("ce"):
+            os.environ["B200_DDP_CE"] = "1"         # peers' slices by copy engine, local reduction kernel
         mode_ddp(tmp)
     elif mode.startswith("fsdp"):
         parts = mode.split(":")
