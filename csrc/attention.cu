@@ -6,16 +6,23 @@
 // it serves Q, K and V tiles (column offsets hd*64, h + hd*64, 2h + hd*64).  Output is written in
 // [B, S, H, D] order, i.e. the [B*S, h] matrix o_proj consumes.
 //
-// Forward CTA = (q block of 128 rows, head, batch), 6 warps:
-//   warp 0     TMA producer: Q once, K/V tiles through 2-stage rings
+// Both kernels are persistent: one CTA per SM walks a boustrophedon list of work items ordered heaviest
+// first (snake_tile), so barriers / TMEM / tensor maps are set up once and every ring index and mbarrier
+// phase derives from running counters.
+//
+// Forward work item = (q block of 128 rows, head, batch); CTA = 18 warps:
+//   warp 0     TMA producer: Q (double buffered across items), K/V tiles through 2-stage rings
 //   warp 1     MMA issuer:   S_j = Q K_j^T  (TMEM, double buffered)  and  O_j = P_j V_j (TMEM, double buffered)
 //   warps 2-17 softmax: four threads per query row, each owning 32 of the 128 score columns (four warps
 //              per scheduler: measured, one or two cannot hide the fixed-latency dependency stalls).  tcgen05.ld S ->
-//              online softmax in the exp2 domain (row max exchanged once per tile through smem) ->
-//              dropout -> bf16 P tile written to 128B-swizzled smem (A operand of P V) -> running O kept
-//              in registers: o = o * alpha + O_j (no TMEM rescale pass).
-// Backward CTA = (kv block, head, batch) looping over q blocks i >= j; five MMAs per pair:
+//              online softmax in the exp2 domain on RAW scores (scale folded into the exponent FFMA2, one
+//              MUFU.EX2 per element, row max exchanged once per tile through smem) -> dropout as compare +
+//              select on the Philox words -> bf16 P tile written to 128B-swizzled smem (A operand of P V)
+//              -> running O kept in registers: o = o * alpha + O_j (no TMEM rescale pass).
+// Backward work item = (kv block, head, batch) looping over q blocks i >= j; five MMAs per pair:
 //   S = Q K^T, dP = dO V^T, dV += P~^T dO, dK += dS^T Q, dQ_i = dS K  (dQ reduced with red.global.add.f32)
+// S / dP of pair i+1 are issued as soon as pair i's are in registers; P~ / dS (smem) and dQ (TMEM) are double
+// buffered so the other three MMAs of pair i run under the element-wise work of pair i+1.
 // P~ / dS tiles are written once to smem and consumed both K-major (dS K) and MN-major (P~^T dO,
 // dS^T Q) through different UMMA descriptors -- no transposes.
 //
