@@ -201,6 +201,21 @@ class FusedGPTEngine:
         K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=epi, split_k=split, tile_n=bn,
                max_ctas=self.max_ctas, M=n_out, N=k_in, K=dy.shape[0])
 
+    def _wave_split(self, tiles: int, k_blocks: int) -> int:
+        """Split-K factor for a reduce-add GEMM of ``tiles`` 256-row pair tiles: the one whose tiles x split
+        work units fill whole waves of CTA pairs best (1 % per extra split for the added reduce-add traffic;
+        every unit keeps at least 16 K blocks)."""
+        pairs = max(1, (self.max_ctas if 0 < self.max_ctas < self.sm_count else self.sm_count) // 2)
+        best, best_score = 1, -1.0
+        for s in range(1, 17):
+            if s > 1 and k_blocks // s < 16:
+                break
+            units = tiles * s
+            score = units / (((units + pairs - 1) // pairs) * pairs) - 0.01 * (s - 1)
+            if score > best_score + 1e-9:
+                best, best_score = s, score
+        return best
+
     def _weights(self, l: int) -> LayerWeights:
         return self.weights_hook(l) if self.weights_hook is not None else self.w_layers[l]
 
@@ -284,8 +299,10 @@ class FusedGPTEngine:
             if with_grad:
                 # dX chunk: [rows, V] x [V, h] has only rows/128 * h/256 output tiles (21 for 896 x 768) but a
                 # 50k-long contraction, so split K across the SMs and reduce in fp32 (cast to bf16 afterwards)
-                tiles = ((r1 - r0 + 127) // 128) * ((ws.dxnf32.shape[1] + 255) // 256)
-                split = max(1, min(16, self.sm_count // max(tiles, 1)))
+                # The split that fills whole waves of CTA pairs wins (measured, benchmarks/bench_splitk.py:
+                # 4096 x 768 has 48 pair tiles on 74 pairs -- split 1: 250 us, split 3 (144 units, 1.95 waves): 199 us)
+                tiles = ((r1 - r0 + 255) // 256) * ((ws.dxnf32.shape[1] + 255) // 256)
+                split = self._wave_split(tiles, (V + 63) // 64)
                 K.gemm(logits, w, ws.dxnf32[r0:r1], b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split, tile_n=256,
                        max_ctas=self.max_ctas, K=V)
                 K.gemm(logits, ws.xnf[r0:r1], self.g_emb, a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, tile_n=256,
