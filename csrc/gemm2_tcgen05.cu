@@ -618,10 +618,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           }
           fence_proxy_async_smem();
           named_bar_sync(1, kEpiThreads);
+          // C = [dgate | dup] is 2 * half_n wide, so a unit past column half_n (last tile of an intermediate size
+          // that is not a multiple of the tile width) is NOT clipped by the tensor map: its dgate store would
+          // land on the first dup columns.  Such units are dropped here (their loads were harmless).
           if (epi_leader) {
-            tma_store_2d(&tma_c, smem_epi + (2 * pr) * kEpiBuf, n0 + c * 64, m0);
-            tma_store_2d(&tma_c, smem_epi + (2 * pr + 1) * kEpiBuf, p.half_n + n0 + c * 64, m0);
-            tma_store_commit();
+            if (n0 + c * 64 < p.N) {
+              tma_store_2d(&tma_c, smem_epi + (2 * pr) * kEpiBuf, n0 + c * 64, m0);
+              tma_store_2d(&tma_c, smem_epi + (2 * pr + 1) * kEpiBuf, p.half_n + n0 + c * 64, m0);
+            }
+            tma_store_commit();   // one (possibly empty) group per unit: the slot-reuse waits count groups
           }
         }
       }

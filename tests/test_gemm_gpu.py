@@ -140,11 +140,13 @@ def test_gemm_resid_dropout_epilogue():
     assert (dy.float() - g * mask.float() / (1 - p)).abs().max().item() < 0.05
 
 
-def test_gemm_swiglu_epilogues():
+@pytest.mark.parametrize("M,h,I", [(512, 256, 1024), (256, 64, 384), (300, 128, 640), (1000, 192, 128)])
+def test_gemm_swiglu_epilogues(M, h, I):
+    """I = 384 / 640 / 128: intermediate sizes that are not a multiple of the 256-wide tile -- the last tile's
+    columns beyond I must neither be read as gate nor written over the first dup columns."""
     from distributed_llm_trainer_b200.ops import kernels as k
 
     torch.manual_seed(5)
-    M, h, I = 512, 256, 1024
     x, w = _mk((M, h)), _mk((2 * I, h), 0.05)   # rows [0,I) gate, [I,2I) up
     gu = torch.zeros(M, 2 * I, device="cuda", dtype=torch.bfloat16)
     act = torch.zeros(M, I, device="cuda", dtype=torch.bfloat16)
