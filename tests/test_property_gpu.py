@@ -184,3 +184,79 @@ def test_engine_matches_torch_on_ragged_configs(heads, layers, inter128, vocab, 
         if err > 0.1:
             bad.append((n, round(err, 3)))
     assert not bad, f"cfg h={64 * heads} L={layers} I={128 * inter128} V={vocab} B={batch} S={seq}: {bad}"
+
+
+@settings(**_SETTINGS)
+@given(m=st.integers(1, 900), n8=st.integers(1, 160), k8=st.integers(1, 80), p=st.sampled_from([0.0, 0.1]),
+       pair=st.booleans(), tile=st.sampled_from([0, 256, 384]))
+def test_gemm_resid_dropout_any_shape(m, n8, k8, p, pair, tile):
+    from distributed_llm_trainer_b200.ops import kernels as k
+
+    n, kk = 8 * n8, 8 * k8
+    if tile == 384:
+        n = max(384, n // 384 * 384)
+        pair = True
+    torch.manual_seed(m + n + kk)
+    a, b = _bf((m, kk), 0.5), _bf((n, kk), 0.1)
+    res = torch.randn(m, n, device="cuda")
+    rng = torch.tensor([m, n], dtype=torch.int64, device="cuda")
+    out = torch.full((m, n), float("nan"), device="cuda")
+    k.gemm(a, b, out, epilogue=k.EPI_RESID_DROPOUT, residual=res, dropout_p=p, rng_state=rng, rng_stream=7, pair=pair,
+           tile_n=tile if pair else 0)
+    mask = torch.ones(m, n, dtype=torch.uint8, device="cuda")
+    if p > 0:
+        k.dropout_mask(mask, p, rng, 7)
+    torch.cuda.synchronize()
+    ref = res + (a.float() @ b.float().t()) * mask.float() / (1 - p)
+    err = (out - ref).abs().max().item()
+    tol = 0.02 * math.sqrt(kk) + 1e-3 * ref.abs().max().item()
+    assert err <= tol, f"resid+dropout {m}x{n}x{kk} p={p} pair={pair} tile={tile}: {err} > {tol}"
+
+
+@settings(**_SETTINGS)
+@given(b=st.integers(1, 3), s=st.integers(1, 300), heads=st.integers(1, 4), pair=st.booleans())
+def test_gemm_rope_any_shape(b, s, heads, pair):
+    from distributed_llm_trainer_b200.ops import kernels as k
+    from distributed_llm_trainer_b200.ops import reference as R
+
+    h, m = 64 * heads, b * s
+    torch.manual_seed(m + h)
+    x, w = _bf((m, h)), _bf((3 * h, h), 0.05)
+    cos, sin = R.rope_tables(s, 64, device="cuda")
+    out = torch.full((m, 3 * h), float("nan"), device="cuda", dtype=torch.bfloat16)
+    k.gemm(x, w, out, epilogue=k.EPI_ROPE_BF16, rope_cos=cos, rope_sin=sin, seq_len=s, rope_cols=2 * h, pair=pair)
+    torch.cuda.synchronize()
+    ref = R.rope_packed(x.float() @ w.float().t(), cos, sin, s, 2 * h)
+    err = (out.float() - ref).abs().max().item()
+    assert err <= 0.02 * math.sqrt(h) + 0.05 * ref.abs().max().item() * 2 ** -7, f"rope {b}x{s}x{h} pair={pair}: {err}"
+
+
+@settings(**dict(_SETTINGS, max_examples=10 * _SCALE))
+@given(b=st.integers(1, 3), s=st.integers(1, 400), h=st.integers(1, 3), p=st.sampled_from([0.0, 0.1]))
+def test_attention_bwd_rope_any_shape(b, s, h, p):
+    """The engine's entry point (delta + zero-fill fused, dQ cast + inverse RoPE fused) against the plain one."""
+    from distributed_llm_trainer_b200.ops import kernels as k
+    from distributed_llm_trainer_b200.ops import reference as R
+
+    torch.manual_seed(b * 31 + s + h)
+    hd = h * 64
+    qkv, dout = _bf((b * s, 3 * hd), 0.8), _bf((b * s, hd), 0.5)
+    rng = torch.tensor([3, 1], dtype=torch.int64, device="cuda")
+    out = torch.zeros(b * s, hd, device="cuda", dtype=torch.bfloat16)
+    lse = torch.zeros(b, h, s, device="cuda")
+    k.attn_fwd(qkv, out, lse, b, s, h, p, rng, 2)
+    cos, sin = R.rope_tables(s, 64, device="cuda")
+    res = []
+    for fused in (False, True):
+        dqkv = torch.zeros(b * s, 3 * hd, device="cuda", dtype=torch.bfloat16)
+        delta = torch.full((b, h, s), float("nan"), device="cuda")
+        dq_acc = torch.full((b * s, hd), float("nan"), device="cuda")
+        if fused:
+            k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, b, s, h, p, rng, 2, rope_cos=cos, rope_sin=sin)
+        else:
+            k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, b, s, h, p, rng, 2)
+            k.rope_inplace(dqkv, cos, sin, 2 * hd, s, inverse=True)
+        torch.cuda.synchronize()
+        res.append(dqkv.float())
+    err = (res[0] - res[1]).abs().max().item()
+    assert err <= 0.02 * max(1.0, res[0].abs().max().item()), f"{b}x{s}x{h} p={p}: {err}"
