@@ -10,7 +10,8 @@ Parity targets
   ``load_yaml_config`` turns them into the dataclasses and explicit CLI flags override the file.
 
 New fields (all optional, defaults keep reference behaviour): ``seed``, ``metrics_path``,
-``resume_from``/``eval_interval`` are live instead of dead, ``backend``.
+``resume_from``/``eval_interval`` are live instead of dead, ``backend``, the tracing switches
+``profile_steps`` / ``profile_start`` / ``profile_dir`` / ``nvtx``.
 """
 from __future__ import annotations
 
@@ -45,6 +46,11 @@ class TrainingConfig:
     eval_batches: int = 4
     backend: str = "nccl"                # "gloo" for CPU multi-process tests
     adam_eps: float = 1e-8
+    # tracing (utils/tracing.py): torch.profiler window, NVTX ranges
+    profile_steps: int = 0
+    profile_start: int = 5
+    profile_dir: str = "profiles_run"
+    nvtx: bool = False
 
     def to_dict(self) -> Dict[str, Any]:
         return asdict(self)

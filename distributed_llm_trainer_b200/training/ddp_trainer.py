@@ -37,6 +37,7 @@ from ..models import GPT, GPTConfig, count_parameters
 from ..utils.checkpoint import atomic_save, config_to_plain, find_latest_checkpoint, load_checkpoint_file
 from ..utils.dist import init_distributed
 from ..utils.logging import MetricsLogger, format_ddp_line
+from ..utils.tracing import StepTracer
 from .config import TrainingConfig, load_yaml_config
 from .lr import cosine_lr
 
@@ -330,6 +331,10 @@ def build_parser() -> argparse.ArgumentParser:
     p.add_argument("--checkpoint_dir", type=str, default=None)
     p.add_argument("--metrics_path", type=str, default=None)
     p.add_argument("--backend", type=str, default=None, choices=["nccl", "gloo"])
+    p.add_argument("--profile_steps", type=int, default=None, help="torch.profiler over this many steps")
+    p.add_argument("--profile_start", type=int, default=None, help="first profiled step (default 5)")
+    p.add_argument("--profile_dir", type=str, default=None, help="where trace_rank*.json / kernels_rank*.txt go")
+    p.add_argument("--nvtx", action="store_true", help="NVTX range per optimizer step")
     # tiny-model overrides so the CPU plumbing run finishes in seconds
     for name in ("vocab_size", "hidden_size", "num_layers", "num_heads", "max_seq_len"):
         p.add_argument(f"--{name}", type=int, default=None)
@@ -370,10 +375,12 @@ def resolve_configs(args, fsdp: bool = False):
         model_cfg.gradient_checkpointing = True
     for k in ("batch_size", "max_steps", "mixed_precision", "resume_from", "seed", "gradient_accumulation_steps",
               "warmup_steps", "learning_rate", "log_interval", "save_interval", "eval_interval", "checkpoint_dir",
-              "metrics_path", "backend"):
+              "metrics_path", "backend", "profile_steps", "profile_start", "profile_dir"):
         v = getattr(args, k, None)
         if v is not None:
             setattr(train_cfg, k, v)
+    if getattr(args, "nvtx", False):
+        train_cfg.nvtx = True
     train_cfg.max_seq_len = model_cfg.max_seq_len
     return model_cfg, train_cfg, fsdp_cfg, extras
 
@@ -400,6 +407,7 @@ def run_training_loop(trainer, dataloader, train_cfg, line_fn, banner: str) -> N
         print(banner)
         print("=" * 60 + "\n")
     metrics = MetricsLogger(train_cfg.metrics_path, enabled=trainer.is_main_process)
+    tracer = StepTracer(train_cfg, rank=getattr(trainer, "rank", 0), device=getattr(trainer, "device", None))
     it = iter(dataloader)
     epoch = 0
     start = time.time()
@@ -415,13 +423,18 @@ def run_training_loop(trainer, dataloader, train_cfg, line_fn, banner: str) -> N
             it = iter(dataloader)
             batch = next(it)
         ids = batch[0] if isinstance(batch, (list, tuple)) else batch
+        tracer.begin(step)
         out = trainer.train_step({"input_ids": ids})
+        tracer.end(step)
         if step % train_cfg.log_interval == 0 and trainer.is_main_process:
             elapsed = max(time.time() - start, 1e-9)
             tps = (out["tokens"] - start_tokens) / elapsed
             print(line_fn(step, out, tps))
-            metrics.log({"step": step, "loss": out["loss"], "lr": out["lr"], "tokens": out["tokens"],
-                         "tokens_per_sec": tps})
+            rec = {"step": step, "loss": out["loss"], "lr": out["lr"], "tokens": out["tokens"], "tokens_per_sec": tps}
+            step_ms = tracer.read_step_ms()     # device time of this step (CUDA events), not in the console line
+            if step_ms is not None:
+                rec["step_ms"] = step_ms
+            metrics.log(rec)
         if train_cfg.eval_interval and step > 0 and step % train_cfg.eval_interval == 0 and hasattr(trainer, "evaluate"):
             ev = []
             ev_it = iter(dataloader)
@@ -438,6 +451,7 @@ def run_training_loop(trainer, dataloader, train_cfg, line_fn, banner: str) -> N
                 metrics.log({"step": step, "eval_loss": val})
         if step > 0 and step % train_cfg.save_interval == 0:
             trainer.save_checkpoint(f"{train_cfg.checkpoint_dir}/step_{step}.pt")
+    tracer.close()
     trainer.save_checkpoint(f"{train_cfg.checkpoint_dir}/final.pt")
     metrics.close()
     return start
