@@ -29,6 +29,7 @@ from __future__ import annotations
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Tuple
 
+import os
 import torch
 import torch.nn.functional as F
 
@@ -126,7 +127,7 @@ class FusedGPTEngine:
         self.rope_cos, self.rope_sin = rope_tables(cfg.max_seq_len, 64, device=self.device)
         self.rng_state = torch.tensor([seed & 0x7FFFFFFFFFFFFFFF, 0], dtype=torch.int64, device=self.device)
         self._ws: Dict[Tuple[int, int, bool], _Workspace] = {}
-        self.use_graphs = __import__("os").environ.get("B200_NO_GRAPHS", "0") != "1"   # B200_NO_GRAPHS=1: eager launches (profiling)
+        self.use_graphs = os.environ.get("B200_NO_GRAPHS", "0") != "1"   # B200_NO_GRAPHS=1: eager launches (profiling)
         # epilogue-fusion switch (A/B-able): SwiGLU' inside the down-proj dgrad GEMM (CTA-pair kernel: gate|up
         # prefetched by TMA into the staging ring) vs GEMM + streaming kernel
         self.fuse_swiglu_bwd = True

@@ -9,6 +9,7 @@ from __future__ import annotations
 import ctypes as C
 from typing import Optional
 
+import os
 import torch
 
 from . import _lib
@@ -20,7 +21,7 @@ launch_count = 0
 # route plain / fp32-accumulate GEMMs to the CTA-pair kernel (set False to A/B against the 1-CTA kernel)
 use_pair_kernel = True
 # which attention-forward kernel attn_fwd() launches (see its docstring)
-attn_fwd_impl = int(__import__("os").environ.get("B200_ATTN_FWD", "1"))
+attn_fwd_impl = int(os.environ.get("B200_ATTN_FWD", "1"))
 
 
 class GemmArgs(C.Structure):

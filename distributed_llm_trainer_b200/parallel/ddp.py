@@ -23,6 +23,7 @@ Two implementations of what the reference gets from ``torch.nn.parallel.Distribu
 from __future__ import annotations
 
 from contextlib import contextmanager
+import os
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -124,12 +125,12 @@ class NVLinkGradSync:
         # that micro-step).  Default off: measured on 2xB200 with the small model the whole reduction is ~0.5 ms
         # of a 52 ms step, and running it under the backward GEMMs costs them more (52.8 ms with overlap and 32
         # comm CTAs, 62.4 ms with 4, vs 51.7 ms reducing after the backward) -- profiles/ddp_overlap_ab.md.
-        self.overlap = __import__("os").environ.get("B200_DDP_OVERLAP", "0") == "1"
+        self.overlap = os.environ.get("B200_DDP_OVERLAP", "0") == "1"
         # small grid: shares the SMs with the backward GEMMs it overlaps
-        self.comm_ctas = int(__import__("os").environ.get("B200_DDP_COMM_CTAS", "32"))
+        self.comm_ctas = int(os.environ.get("B200_DDP_COMM_CTAS", "32"))
         # B200_DDP_CE=1: peers' copies of the owned slice come over by copy engine into local scratch and the
         # reduction kernel reads local memory only (no SM time spent waiting on NVLink loads)
-        self.ce = __import__("os").environ.get("B200_DDP_CE", "0") == "1"
+        self.ce = os.environ.get("B200_DDP_CE", "0") == "1"
         self._ce_tmp: Optional[List[torch.Tensor]] = None
         self._last = False
         self._overlapped = False

@@ -25,6 +25,7 @@ NO_SHARD (:269-274), bf16 parameters + communication with fp32 sharded master we
 """
 from __future__ import annotations
 
+import os
 from typing import Any, Dict, List, Optional, Tuple
 
 import torch
@@ -165,10 +166,9 @@ class ShardedGPT:
         # no_sync, fsdp_trainer.py:369-384) an avoidable cost: GA x less traffic and GA x fewer barriers.
         # B200_FSDP_ACCUM_LOCAL=0 restores the per-micro-step reduction through two rotating staging buffers
         # (gradient memory / world, the reference's footprint).
-        import os as _os0
         full_bytes = 4 * blk * self.L
         free_b, _tot = torch.cuda.mem_get_info(dev)
-        self.accum_local = (_os0.environ.get("B200_FSDP_ACCUM_LOCAL", "1") != "0" and self.L > 0
+        self.accum_local = (os.environ.get("B200_FSDP_ACCUM_LOCAL", "1") != "0" and self.L > 0
                             and full_bytes < 0.25 * free_b)
         n_stage = self.L if self.accum_local else 2
         self.grad_pool = [SymmetricBuffer(blk, torch.float32, dev) for _ in range(n_stage)]
@@ -179,27 +179,25 @@ class ShardedGPT:
         self._params_ready: Optional[torch.cuda.Event] = None   # recorded after the optimizer step's barrier
         self.max_ctas = 0
         # all-gather fused into the QKV GEMM (B200_FSDP_FUSE_AG=0 gathers those rows with the rest of the unit)
-        import os as _os
-
         self._unit_ptr_cache: Dict[int, Any] = {}
         h = model.config.hidden_size
         self.qkv_len = 3 * h * h
         self.qkv_off = (st.by_name["layers.0.attention.q_proj.weight"].offset - self.units[1].lo) if self.L > 0 else 0
         # Unit all-gathers ride the copy engines by default (B200_FSDP_CE_GATHER=0: the P2P-pull SM kernel).
-        self.ce_gather = _os.environ.get("B200_FSDP_CE_GATHER", "1") != "0"
+        self.ce_gather = os.environ.get("B200_FSDP_CE_GATHER", "1") != "0"
         # Same for the gradient reduce-scatter: copy-engine transfer + local sum (B200_FSDP_CE_RS=0: P2P-pull kernel)
-        self.ce_rs = _os.environ.get("B200_FSDP_CE_RS", "1") != "0"
+        self.ce_rs = os.environ.get("B200_FSDP_CE_RS", "1") != "0"
         self._rs_tmp: Dict[int, List[torch.Tensor]] = {}
-        self.use_graphs = (_os.environ.get("B200_FSDP_GRAPHS", "1") != "0"
-                           and _os.environ.get("B200_NO_GRAPHS", "0") != "1")
+        self.use_graphs = (os.environ.get("B200_FSDP_GRAPHS", "1") != "0"
+                           and os.environ.get("B200_NO_GRAPHS", "0") != "1")
         self._graphs: Dict[Tuple[int, int, float], Any] = {}
         self._plain_calls = 0
         # The fused all-gather GEMM is opt-in (B200_FSDP_FUSE_AG=1): a PREFETCHED gather hides completely under
         # the previous block's compute, the fused one only under its own GEMM -- measured +7 ms / step on the
         # 355M benchmark at 2 GPUs (profiles/fsdp_comm_breakdown.md).  It pays when nothing precedes the GEMM.
-        self.fuse_ag = (_os.environ.get("B200_FSDP_FUSE_AG", "0") != "0" and self.L > 0
+        self.fuse_ag = (os.environ.get("B200_FSDP_FUSE_AG", "0") != "0" and self.L > 0
                         and min(self.unit_part[1:]) >= 16384 and 3 * h >= 256)
-        self.ag_pairs = int(_os.environ.get("B200_FSDP_AG_PAIRS", "2"))
+        self.ag_pairs = int(os.environ.get("B200_FSDP_AG_PAIRS", "2"))
         self._ag_flags = [torch.zeros((3 * h + 127) // 128, dtype=torch.int32, device=dev) for _ in self.gather_pool]
         self._ag_epoch = 0
         # engine bound to hooks

@@ -5,6 +5,7 @@ The reference reports cumulative wall-clock tokens/sec from before the first bat
 benchmarks here use this module instead (SURVEY section 5 'Metrics')."""
 from __future__ import annotations
 
+import os
 import statistics
 import subprocess
 import threading
@@ -65,7 +66,7 @@ class ClockSampler:
 
             N.nvmlInit()
             idx = self.gpu_index
-            vis = [v for v in (__import__("os").environ.get("CUDA_VISIBLE_DEVICES") or "").split(",") if v.strip()]
+            vis = [v for v in (os.environ.get("CUDA_VISIBLE_DEVICES") or "").split(",") if v.strip()]
             if vis and idx < len(vis) and vis[idx].strip().isdigit():
                 idx = int(vis[idx])
             h = N.nvmlDeviceGetHandleByIndex(idx)
