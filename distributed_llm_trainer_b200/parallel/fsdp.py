@@ -128,7 +128,7 @@ class ShardedGPT:
         self.cpu_offload = cpu_offload
         dev = next(model.parameters()).device
         self.device = dev
-        # fp32 master (full-size buffer, only the owned slices are kept current -- see DESIGN.md) + flat layout
+        # flat layout; the full-size fp32 buffer only lives until the shards are cut (release_full_master below)
         self.store = FlatParamStore(model, device=dev, with_grad=False, with_shadow=False)
         st = self.store
         dist.broadcast(st.master, src=0)
@@ -151,7 +151,10 @@ class ShardedGPT:
         # bf16 shard (peers pull from it) and sharded fp32 gradient accumulator
         self.shard_bf16 = SymmetricBuffer(self.shard_total, torch.bfloat16, dev)
         self.grad_shard = torch.zeros(self.shard_total, dtype=torch.float32, device=dev)
+        self.master_shard = torch.zeros(self.shard_total, dtype=torch.float32, device=dev)
+        self.keep_full_master = os.environ.get("B200_FSDP_FULL_MASTER", "0") == "1"
         self._refresh_shard_from_master()
+        self.release_full_master()
         # pools
         blk = max(self.unit_part[1:]) * world if self.L > 0 else ALIGN
         root = self.unit_part[0] * world
@@ -216,11 +219,41 @@ class ShardedGPT:
 
     # ------------------------------------------------------------------------------------------ setup helpers
     def _refresh_shard_from_master(self) -> None:
+        """Full fp32 parameters (materialised) -> this rank's fp32 master shard and bf16 shard."""
         st = self.store
         with torch.no_grad():
             for u, (a, b) in zip(range(len(self.units)), self.ranges):
                 off = self.shard_off[u]
+                self.master_shard[off: off + b - a].copy_(st.master[a:b])
                 self.shard_bf16.local[off: off + b - a].copy_(st.master[a:b])
+
+    # The fp32 master weights are sharded like everything else: outside of checkpoint save / load only
+    # ``master_shard`` (1/N of the model) exists and the module's parameters point at empty storage.
+    # B200_FSDP_FULL_MASTER=1 keeps the full-size buffer resident (module parameters stay readable, owned
+    # slices only are current).
+    def release_full_master(self) -> None:
+        st = self.store
+        if self.keep_full_master or st.master.numel() == 0:
+            return
+        empty = torch.empty(0, dtype=torch.float32, device=self.device)
+        for p in st.params:
+            p.data = empty
+        st.master = empty
+
+    def materialize_full_master(self) -> None:
+        """Re-create the full fp32 buffer with this rank's owned slices filled in (others zero) and point the
+        module's parameters back at it."""
+        st = self.store
+        if st.master.numel() == st.total:
+            if self.keep_full_master:
+                for u, (a, b) in enumerate(self.ranges):
+                    st.master[a:b].copy_(self.master_shard[self.shard_off[u]: self.shard_off[u] + b - a])
+            return
+        st.master = torch.zeros(st.total, dtype=torch.float32, device=self.device)
+        for p, s in zip(st.params, st.slots):
+            p.data = st.master[s.offset: s.offset + s.numel].view(s.shape)
+        for u, (a, b) in enumerate(self.ranges):
+            st.master[a:b].copy_(self.master_shard[self.shard_off[u]: self.shard_off[u] + b - a])
 
     def _views(self, buf: torch.Tensor, l: int, LayerWeights):
         """LayerWeights views into a gathered/staging unit buffer for block l (offsets relative to the unit)."""
@@ -568,7 +601,8 @@ class ShardedGPT:
             if b <= a:
                 continue
             off = self.shard_off[u]
-            K.adamw_step_ptr(st.master.data_ptr(), self.grad_shard.data_ptr() + (off - a) * 4,
+            # every buffer is addressed so that flat element index a lands on this unit's slice of the shard
+            K.adamw_step_ptr(self.master_shard.data_ptr() + (off - a) * 4, self.grad_shard.data_ptr() + (off - a) * 4,
                              opt_state["exp_avg"].data_ptr() + off * 4, opt_state["exp_avg_sq"].data_ptr() + off * 4,
                              self.shard_bf16.local.data_ptr() + (off - a) * 2, opt_state["decay"].data_ptr(), a,
                              a + (b - a + 3) // 4 * 4, opt_state["step"], lr, b1, b2, eps, wd,
@@ -591,8 +625,7 @@ class ShardedGPT:
         if not hasattr(self, "_host"):
             pin = dict(dtype=torch.float32, pin_memory=True)
             master = torch.empty(self.shard_total, **pin)
-            for u, (a, b) in enumerate(self.ranges):
-                master[self.shard_off[u]: self.shard_off[u] + b - a].copy_(self.store.master[a:b])
+            master.copy_(self.master_shard)
             self._host = {"master": master, "grad": torch.empty(self.shard_total, **pin),
                           "bf16": torch.empty(self.shard_total, dtype=torch.bfloat16, pin_memory=True)}
         host = self._host
@@ -604,13 +637,16 @@ class ShardedGPT:
         adamw_reference_(host["master"], host["grad"], m, v, ones, opt_state["step"], lr, b1, b2, eps, wd, 1.0)
         host["bf16"].copy_(host["master"])
         self.shard_bf16.local.copy_(host["bf16"], non_blocking=True)
-        for u, (a, b) in enumerate(self.ranges):                    # keep the device copy of the owned slices current
-            self.store.master[a:b].copy_(host["master"][self.shard_off[u]: self.shard_off[u] + b - a], non_blocking=True)
+        self.master_shard.copy_(host["master"], non_blocking=True)   # device copy of the shard (checkpoints read it)
 
     # ------------------------------------------------------------------------------------------ checkpoints
     def gather_full_master(self) -> None:
+        """Collective: materialise the full fp32 parameters on every rank (module parameters become readable).
+        Call ``release_full_master()`` when done with them."""
         st = self.store
-        _gather_ranges(self.all_ranges, self.world, [st.master[a:b] for a, b in self.ranges], st.master)
+        self.materialize_full_master()
+        pieces = [self.master_shard[self.shard_off[u]: self.shard_off[u] + b - a] for u, (a, b) in enumerate(self.ranges)]
+        _gather_ranges(self.all_ranges, self.world, pieces, st.master)
 
     def gather_flat(self, shard: torch.Tensor) -> torch.Tensor:
         """shard-layout tensor (concatenated per-unit parts) -> full flat tensor."""

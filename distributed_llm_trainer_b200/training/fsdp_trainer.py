@@ -248,6 +248,9 @@ class FSDPTrainer:
                 "fsdp_config": config_to_plain(self.fsdp_config), "extra": extra,
             }, path)
             print(f"Saved checkpoint to {path} (step {self.global_step})")
+        del state
+        if self.sharded is not None:
+            self.sharded.release_full_master()      # back to 1/N of the fp32 parameters per rank
         if self.distributed:
             dist.barrier()
 
@@ -255,6 +258,8 @@ class FSDPTrainer:
         """Every rank reads the file and keeps its own slices (the reference pickles the whole checkpoint
         through ``broadcast_object_list``, fsdp_trainer.py:467-494 / SURVEY K13)."""
         ckpt = load_checkpoint_file(path, map_location="cpu")
+        if self.sharded is not None:
+            self.sharded.materialize_full_master()  # module parameters need storage to load into
         self.model.load_state_dict(ckpt["model"])
         opt = self.optimizer
         if self.sharded is not None:
@@ -270,6 +275,7 @@ class FSDPTrainer:
             self.opt_state["step"] = full.step_count
             opt.step_count = full.step_count
             del full
+            sh.release_full_master()
         else:
             opt.load_state_dict(ckpt["optimizer"])
             if self.engine is not None:

@@ -145,7 +145,11 @@ def mode_fsdp(tmp, strategy, offload=False):
     tr = FSDPTrainer(GPTConfig(**CFG), tcfg, fcfg)
     rank, world = tr.rank, tr.world_size
     solo = single_process_reference("fsdp", world, ga, steps, strategy)
+    if getattr(tr, "sharded", None) is not None:
+        tr.sharded.gather_full_master()           # sharded fp32 master: materialise to read the initial weights
     solo.model.load_state_dict(tr.model.state_dict())
+    if getattr(tr, "sharded", None) is not None:
+        tr.sharded.release_full_master()
     if solo.engine is not None:
         solo.engine.store.refresh_shadow()
     data = [batches(steps, 2 * ga, seed=200 + r) for r in range(world)]
@@ -157,8 +161,14 @@ def mode_fsdp(tmp, strategy, offload=False):
         assert abs(lt.item() / world - ref["loss"]) < (2e-2 if GPU else 1e-5) * abs(ref["loss"]), (lt.item() / world, ref)
     path = os.path.join(tmp, f"fsdp_{strategy}.pt")
     tr.save_checkpoint(path)          # gathers full fp32 parameters + optimizer state (collective)
+    sharded = getattr(tr, "sharded", None)
+    if sharded is not None:           # fp32 master weights are sharded: outside of save / load the module's
+        assert all(p.numel() == 0 for p in tr.model.parameters())      # parameters hold no storage
+        sharded.gather_full_master()
     for (n, p), (_, q) in zip(tr.model.named_parameters(), solo.model.named_parameters()):
         close(p.detach(), q.detach(), 2e-2 if GPU else 1e-5, n)
+    if sharded is not None:
+        sharded.release_full_master()
     ck = torch.load(path, map_location="cpu", weights_only=False)
     assert ck["fsdp_config"]["sharding_strategy"] == strategy
     assert set(ck["optimizer"]["state"]) == {n for n, _ in solo.model.named_parameters()}
