@@ -866,10 +866,10 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.out = (__nv_bfloat16*)out; p.lse = lse;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[kMaxDevices] = {};   // the attribute is per device
+  if (!configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::kTotal));
-    configured = true;
+    configured[current_device()] = true;
   }
   // persistent: one CTA per SM walks its share of the (q tile, head, batch) list
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;
@@ -925,10 +925,10 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[kMaxDevices] = {};   // the attribute is per device
+  if (!configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal));
-    configured = true;
+    configured[current_device()] = true;
   }
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
   dim3 grid(tiles < sm_count() ? tiles : sm_count());

@@ -294,10 +294,10 @@ extern "C" int b200_attn_fwd2(const void* qkv, void* out, float* lse, int batch,
   Params p{};
   p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.out = (__nv_bfloat16*)out; p.lse = lse;
-  static bool configured = false;
-  if (!configured) {
+  static bool configured[kMaxDevices] = {};   // the attribute is per device
+  if (!configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem::kTotal));
-    configured = true;
+    configured[current_device()] = true;
   }
   dim3 grid(((seq + kBlk - 1) / kBlk) * heads * batch);
   attn_fwd2_kernel<<<grid, kThreads, Smem::kTotal, reinterpret_cast<cudaStream_t>(stream)>>>(tm, p);

@@ -276,6 +276,139 @@ reduce_scatter_f32_accum_kernel(PeerTable srcs, float* __restrict__ dst, long lo
   }
 }
 
+
+// ------------------------------------------------------------------------------------------------------------
+// Chunk-table kernels: the optimizer side of the fused reduce-scatter.  A rank's owned parameters are a list of
+// short contiguous runs (128-row slabs of the weight matrices, whole norm vectors); the host flattens them into
+// chunks of <= 4096 elements so that ONE launch covers all of them (one launch per run would be ~100 tiny
+// kernels per step).  Offsets are in elements.
+//   g   global flat index of the chunk's first element (weight-decay table lookup)
+//   pg  offset into the local fp32 master / gradient arrays
+//   mv  offset into the local AdamW moment arrays
+//   sh  offset into the destination bf16 parameter buffer(s)
+//   dst rank whose bf16 buffer receives the updated parameters, or -1 = every rank (DDP replicas)
+// ------------------------------------------------------------------------------------------------------------
+struct Chunk {
+  long long g, pg, mv, sh;
+  int n, dst;
+};
+static_assert(sizeof(Chunk) == sizeof(b200_chunk), "b200_chunk layout");
+
+__device__ __forceinline__ float block_sum_256(float acc) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+  __shared__ float sh[8];
+  if ((threadIdx.x & 31) == 0) sh[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  float t = 0.f;
+  if (threadIdx.x == 0)
+    for (int i = 0; i < 8; ++i) t += sh[i];
+  return t;
+}
+
+// out[0] += sq_scale * sum over the chunks of grad^2
+__global__ void __launch_bounds__(256)
+sumsq_chunks_kernel(const float* __restrict__ grad, const Chunk* __restrict__ ch, int nch, float* __restrict__ out,
+                    float sq_scale) {
+  float acc = 0.f;
+  for (int c = blockIdx.x; c < nch; c += gridDim.x) {
+    const Chunk k = ch[c];
+    const float4* src = reinterpret_cast<const float4*>(grad + k.pg);
+    for (int i = threadIdx.x; i < (k.n >> 2); i += 256) {
+      const float4 a = src[i];
+      acc += a.x * a.x + a.y * a.y + a.z * a.z + a.w * a.w;
+    }
+  }
+  const float t = block_sum_256(acc);
+  if (threadIdx.x == 0) atomicAdd(out, t * sq_scale);
+}
+
+// AdamW over the chunks; the bf16 result goes to rank `dst`'s parameter buffer (or to every rank's), and the
+// gradient is cleared in the same pass (zero_grad) so the next step's reduce-adds start from zero.
+__global__ void __launch_bounds__(256)
+adamw_chunks_kernel(float* __restrict__ master, float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
+                    PeerTable shadows, int world, int rank, const uint8_t* __restrict__ decay_chunks,
+                    const Chunk* __restrict__ ch, int nch, float lr, float beta1, float beta2, float eps, float wd,
+                    float step_size, float inv_sqrt_bc2, const float* __restrict__ grad_scale, int zero_grad) {
+  const float gs = grad_scale ? *grad_scale : 1.f;
+  for (int c = blockIdx.x; c < nch; c += gridDim.x) {
+    const Chunk k = ch[c];
+    for (int i = threadIdx.x; i < (k.n >> 2); i += 256) {
+      const long long e = 4LL * i;
+      float4 p = *reinterpret_cast<const float4*>(master + k.pg + e);
+      const float4 g = *reinterpret_cast<const float4*>(grad + k.pg + e);
+      float4 mm = *reinterpret_cast<const float4*>(m + k.mv + e);
+      float4 vv = *reinterpret_cast<const float4*>(v + k.mv + e);
+      const float decay = decay_chunks[(k.g + e) >> 7] ? 1.f - lr * wd : 1.f;
+      float* pp = reinterpret_cast<float*>(&p);
+      const float* gg = reinterpret_cast<const float*>(&g);
+      float* pm = reinterpret_cast<float*>(&mm);
+      float* pv = reinterpret_cast<float*>(&vv);
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float ge = gg[q] * gs;
+        pm[q] = beta1 * pm[q] + (1.f - beta1) * ge;
+        pv[q] = beta2 * pv[q] + (1.f - beta2) * ge * ge;
+        pp[q] = pp[q] * decay - step_size * (pm[q] / (sqrtf(pv[q]) * inv_sqrt_bc2 + eps));
+      }
+      *reinterpret_cast<float4*>(master + k.pg + e) = p;
+      *reinterpret_cast<float4*>(m + k.mv + e) = mm;
+      *reinterpret_cast<float4*>(v + k.mv + e) = vv;
+      if (zero_grad) *reinterpret_cast<float4*>(grad + k.pg + e) = make_float4(0.f, 0.f, 0.f, 0.f);
+      const uint2 s = make_uint2(pack_bf16x2(pp[0], pp[1]), pack_bf16x2(pp[2], pp[3]));
+      if (k.dst >= 0) {
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(shadows.p[k.dst]) + k.sh + e) = s;
+      } else {
+        for (int r = 0; r < world; ++r)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(shadows.p[(rank + r) % world]) + k.sh + e) = s;
+      }
+    }
+  }
+}
+
+// Small tensors (norm weights) accumulate in every rank's own buffer; their owner pulls the peers' copies:
+// dst[pg ..] = sum_r src_r[g ..], and the peers' copies are cleared remotely for the next step (zero_remote).
+__global__ void __launch_bounds__(256)
+pull_reduce_chunks_kernel(PeerTable srcs, float* __restrict__ dst, const Chunk* __restrict__ ch, int nch, int rank,
+                          int world, int zero_remote) {
+  for (int c = blockIdx.x; c < nch; c += gridDim.x) {
+    const Chunk k = ch[c];
+    for (int i = threadIdx.x; i < (k.n >> 2); i += 256) {
+      const long long e = 4LL * i;
+      float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+      for (int r = 0; r < world; ++r) {
+        float* src = reinterpret_cast<float*>(srcs.p[(rank + r) % world]) + k.g + e;
+        const float4 a = ld_peer_f4(src);
+        s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
+        if (zero_remote && r != 0) *reinterpret_cast<float4*>(src) = make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      *reinterpret_cast<float4*>(dst + k.pg + e) = s;
+    }
+  }
+}
+
+// Embedding-gradient scatter with owner-directed rows: token row t adds dx[t] into row ids[t] of the embedding
+// gradient held by the rank that owns that row's 128-row slab (red.global.add over NVLink for remote owners).
+__global__ void embed_bwd_rs_kernel(const int64_t* __restrict__ ids, const float* __restrict__ dx, PeerTable owner_base,
+                                    int rows, int hidden, int vocab, int world, int slabs, int rot) {
+  const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+  if (row >= rows) return;
+  const long long id = ids[row];
+  if (id < 0 || id >= vocab) return;
+  const int s = int(id >> 7);
+  const int op = int(((long long)s * world) / slabs);
+  int o = op + rot;
+  if (o >= world) o -= world;
+  const int first = (op * slabs + world - 1) / world;
+  const float4* src = reinterpret_cast<const float4*>(dx + size_t(row) * hidden);
+  float* dstp = reinterpret_cast<float*>(owner_base.p[o]) + (size_t(id) - (size_t(first) << 7)) * hidden;
+  for (int i = threadIdx.x & 31; i < hidden / 4; i += 32) {
+    const float4 a = src[i];
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dstp + 4 * i), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w)
+                 : "memory");
+  }
+}
+
 static int fill_table(PeerTable* t, const void* const* host_ptrs, int world) {
   B200_REQUIRE(world >= 1 && world <= kMaxRanks, "comm: world size %d out of range (max %d)", world, kMaxRanks);
   for (int i = 0; i < kMaxRanks; ++i) t->p[i] = i < world ? const_cast<void*>(host_ptrs[i]) : nullptr;
@@ -404,6 +537,59 @@ int b200_reduce_scatter_bf16_accum(const void* const* full_grad_ptrs, float* dst
   if (blocks > cap) blocks = cap;
   reduce_scatter_bf16_accum_kernel<<<(unsigned)blocks, 512, 0, STREAM(stream)>>>(srcs, dst_shard, src_offset / 8, n / 8,
                                                                                   scale, rank, world);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_sumsq_chunks(const float* grad, const b200_chunk* chunks_dev, int n_chunks, float* out, float sq_scale,
+                      void* stream) {
+  if (n_chunks <= 0) return 0;
+  int blocks = n_chunks < sm_count() * 8 ? n_chunks : sm_count() * 8;
+  sumsq_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(grad, reinterpret_cast<const Chunk*>(chunks_dev), n_chunks, out,
+                                                         sq_scale);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg_sq, const void* const* param_ptrs,
+                      int rank, int world, const uint8_t* decay_chunks, const b200_chunk* chunks_dev, int n_chunks,
+                      int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                      const float* grad_scale, int zero_grad, int max_ctas, void* stream) {
+  if (n_chunks <= 0) return 0;
+  PeerTable sh;
+  if (int rc = fill_table(&sh, param_ptrs, world)) return rc;
+  const double bc1 = 1.0 - pow((double)beta1, (double)step);
+  const double bc2 = 1.0 - pow((double)beta2, (double)step);
+  int cap = max_ctas > 0 ? max_ctas : sm_count() * 8;
+  int blocks = n_chunks < cap ? n_chunks : cap;
+  adamw_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(master, grad, exp_avg, exp_avg_sq, sh, world, rank, decay_chunks,
+                                                         reinterpret_cast<const Chunk*>(chunks_dev), n_chunks, lr, beta1,
+                                                         beta2, eps, weight_decay, (float)(lr / bc1),
+                                                         (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_pull_reduce_chunks(const void* const* src_ptrs, float* dst, const b200_chunk* chunks_dev, int n_chunks,
+                            int rank, int world, int zero_remote, void* stream) {
+  if (n_chunks <= 0) return 0;
+  PeerTable srcs;
+  if (int rc = fill_table(&srcs, src_ptrs, world)) return rc;
+  int blocks = n_chunks < sm_count() * 2 ? n_chunks : sm_count() * 2;
+  pull_reduce_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(srcs, dst, reinterpret_cast<const Chunk*>(chunks_dev),
+                                                               n_chunks, rank, world, zero_remote);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_embed_bwd_rs(const int64_t* ids, const float* dx, const void* const* owner_base, int rows, int hidden,
+                      int vocab, int world, int rot, void* stream) {
+  B200_REQUIRE(hidden % 4 == 0, "embed_bwd_rs: hidden must be a multiple of 4");
+  PeerTable ob;
+  if (int rc = fill_table(&ob, owner_base, world)) return rc;
+  const int slabs = (vocab + 127) / 128;
+  const int r = ((rot % world) + world) % world;
+  embed_bwd_rs_kernel<<<(rows + 7) / 8, 256, 0, STREAM(stream)>>>(ids, dx, ob, rows, hidden, vocab, world, slabs, r);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -13,6 +13,10 @@ namespace b200 {
 const char* last_error();
 void set_error(const char* fmt, ...);
 int sm_count();
+// Per-device one-time configuration (cudaFuncSetAttribute is per device/context): launchers keep a
+// `static bool configured[kMaxDevices]` indexed by current_device().
+constexpr int kMaxDevices = 64;
+int current_device();   // cudaGetDevice clamped into [0, kMaxDevices)
 
 #define B200_CHECK_CUDA(expr)                                                              \
   do {                                                                                     \

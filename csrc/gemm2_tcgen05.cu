@@ -79,6 +79,18 @@ struct Params {
   int ag_pairs;                // CTA pairs that gather instead of multiplying
   int ag_rot;                  // n-tile rotation so tiles over locally owned rows are visited first
   int ag_rank, ag_world;
+  // ---- reduce-scatter fused into the epilogue (OWN instantiations): C's 128-row slabs belong to ranks ---------
+  int own_world, own_slabs, own_rot;   // owner of slab s = ((s * world) / slabs + rot) % world
+};
+
+// One output tensor map per owner (OWN instantiations): map o covers the rows of C that rank o owns, at their
+// address in rank o's memory (peer-mapped over NVLink, or local for o == this rank).
+constexpr int kMaxOwners = 8;
+template <bool OWN>
+struct OwnerMaps {};
+template <>
+struct OwnerMaps<true> {
+  CUtensorMap m[kMaxOwners];
 };
 
 __device__ __forceinline__ void bulk_load_g2s(uint32_t smem_dst, const void* gsrc, uint32_t bytes, uint64_t* bar) {
@@ -115,10 +127,12 @@ __device__ __forceinline__ float sigmoid_f(float x) {
 
 // tma_c: primary output.  tma_x: second tensor -- RESID_DROPOUT: residual (fp32, input); SWIGLU: act (bf16,
 // output); SWIGLU_BWD: saved [gate|up] (bf16, input).
-template <int BNP, bool A_MN, bool B_MN, int EPI, bool AG = false>
+template <int BNP, bool A_MN, bool B_MN, int EPI, bool AG = false, bool OWN = false>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
 gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ CUtensorMap tma_b,
-             const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p) {
+             const __grid_constant__ CUtensorMap tma_c, const __grid_constant__ CUtensorMap tma_x, const Params p,
+             const __grid_constant__ OwnerMaps<OWN> om) {
+  static_assert(!OWN || EPI == EPI_F32_ATOMIC, "owner-directed output needs the reduce-add epilogue");
   using C = Cfg<BNP, EPI>;
   constexpr int kStages = C::kStages;
   constexpr int NB = C::kEpiBufs;
@@ -496,7 +510,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
 #pragma unroll
           for (int cc = 0; cc < 4; ++cc)
             st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
-          stage_end(&tma_c, n0 + c * 32, m0, EPI == EPI_F32_ATOMIC);
+          if constexpr (OWN) {
+            // GEMM -> reduce-scatter in one kernel: this CTA's 128 rows are one slab of C; its owner's map
+            // (peer memory over NVLink unless the owner is this rank) takes the reduce-add.  Rows beyond M
+            // belong to nobody (the per-owner maps clip the last slab).
+            fence_proxy_async_smem();
+            named_bar_sync(1, kEpiThreads);
+            if (epi_leader) {
+              if (m0 < p.M) {
+                const int s = m0 >> 7;
+                const int op = (s * p.own_world) / p.own_slabs;             // owner before rotation
+                int o = op + p.own_rot;
+                if (o >= p.own_world) o -= p.own_world;
+                const int first = (op * p.own_slabs + p.own_world - 1) / p.own_world;   // its first slab
+                tma_reduce_add_2d(&om.m[o], smem_epi + (g % NB) * kEpiBuf, n0 + c * 32, m0 - (first << 7));
+              }
+              tma_store_commit();   // one (possibly empty) group per unit: the slot-reuse waits count groups
+            }
+            ++g;
+          } else {
+            stage_end(&tma_c, n0 + c * 32, m0, EPI == EPI_F32_ATOMIC);
+          }
         }
       } else if constexpr (EPI == EPI_RESID_DROPOUT) {
 #pragma unroll 1
@@ -642,16 +676,18 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   }
 }
 
-template <int BNP, bool A_MN, bool B_MN, int EPI, bool AG = false>
+// cudaFuncSetAttribute is per device: remember which devices have this instantiation configured.
+template <int BNP, bool A_MN, bool B_MN, int EPI, bool AG = false, bool OWN = false>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const CUtensorMap& tx,
-                  const Params& p, int grid, cudaStream_t stream) {
-  auto kfn = gemm2_kernel<BNP, A_MN, B_MN, EPI, AG>;
-  static bool configured = false;
-  if (!configured) {
+                  const Params& p, int grid, cudaStream_t stream, const OwnerMaps<OWN>& om = OwnerMaps<OWN>{}) {
+  auto kfn = gemm2_kernel<BNP, A_MN, B_MN, EPI, AG, OWN>;
+  static bool configured[kMaxDevices] = {};
+  const int dev = current_device();
+  if (!configured[dev]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg<BNP, EPI>::kSmemTotal));
-    configured = true;
+    configured[dev] = true;
   }
-  kfn<<<grid, kThreads, Cfg<BNP, EPI>::kSmemTotal, stream>>>(ta, tb, tc, tx, p);
+  kfn<<<grid, kThreads, Cfg<BNP, EPI>::kSmemTotal, stream>>>(ta, tb, tc, tx, p, om);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -689,16 +725,34 @@ static int dispatch_epi(int epi, bool a_mn, bool b_mn, const CUtensorMap& ta, co
 
 using namespace b200;
 
-static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stream_);
+static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, const b200_rs_args* rs, void* stream_);
 
-extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) { return run_gemm2(a, nullptr, stream_); }
+extern "C" int b200_gemm2_bf16(const b200_gemm_args* a, void* stream_) { return run_gemm2(a, nullptr, nullptr, stream_); }
 
 extern "C" int b200_gemm2_ag_bf16(const b200_gemm_args* a, const b200_ag_args* ag, void* stream_) {
   B200_REQUIRE(ag != nullptr, "gemm2_ag: null all-gather arguments");
-  return run_gemm2(a, ag, stream_);
+  return run_gemm2(a, ag, nullptr, stream_);
 }
 
-static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stream_) {
+extern "C" int b200_gemm2_rs_bf16(const b200_gemm_args* a, const b200_rs_args* rs, void* stream_) {
+  B200_REQUIRE(rs != nullptr, "gemm2_rs: null reduce-scatter arguments");
+  return run_gemm2(a, nullptr, rs, stream_);
+}
+
+extern "C" int b200_slab_owner(int slab, int slabs, int world, int rot) {
+  if (slabs <= 0 || world <= 0 || slab < 0 || slab >= slabs) return -1;
+  return int(((long long)slab * world / slabs + rot) % world);
+}
+
+extern "C" int b200_owner_slab_range(int owner, int slabs, int world, int rot, int* first, int* last) {
+  if (slabs <= 0 || world <= 0 || owner < 0 || owner >= world) return -1;
+  const long long op = ((owner - rot) % world + world) % world;
+  *first = int((op * slabs + world - 1) / world);
+  *last = int(((op + 1) * slabs + world - 1) / world);
+  return 0;
+}
+
+static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, const b200_rs_args* rs, void* stream_) {
   using namespace b200::g2;
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   B200_REQUIRE(a != nullptr, "gemm2: null args");
@@ -745,7 +799,10 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stre
   else       rc = make_tmap_2d_bf16(&tb, a->B, a->N, a->K, a->ldb, 64, BK);
   if (rc) return rc;
   const int c_cols = epi == EPI_SWIGLU_BWD ? 2 * a->half_n : a->N;   // SwiGLU': C = [dgate | dup] is 2*half_n wide
-  rc = make_tmap_2d_sw128(&tc, a->C, c_elem, c_cols, a->M, a->ldc, 128);
+  const void* c_base = a->C;
+  if (rs != nullptr && c_base == nullptr && rs->owner_base != nullptr)   // owner-directed output: C itself is optional
+    for (int o = 0; o < rs->world && c_base == nullptr; ++o) c_base = rs->owner_base[o];
+  rc = make_tmap_2d_sw128(&tc, c_base, c_elem, c_cols, a->M, a->ldc, 128);
   if (rc) return rc;
   tx = tc;
   if (epi == EPI_RESID_DROPOUT) rc = make_tmap_2d_sw128(&tx, a->residual, 4, a->N, a->M, a->ldc, 128);
@@ -802,6 +859,29 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, void* stre
     return launch<256, false, false, EPI_ROPE_BF16, true>(ta, tb, tc, tx, p, ag_grid, stream);
   }
   const int grid = int(pairs * 2);
+  if (rs != nullptr) {
+    // GEMM -> reduce-scatter: every 128-row slab of C is reduce-added into its owner's memory
+    B200_REQUIRE(epi == EPI_F32_ATOMIC && a_mn && b_mn && (bnp == 256 || bnp == 128),
+                 "gemm2_rs: instantiated for the wgrad form only (MN-major A and B, fp32 reduce-add epilogue)");
+    B200_REQUIRE(rs->world >= 1 && rs->world <= kMaxOwners && rs->owner_base != nullptr, "gemm2_rs: world must be in [1,%d]", kMaxOwners);
+    const int slabs = (a->M + 127) / 128;
+    const int rot = ((rs->rot % rs->world) + rs->world) % rs->world;
+    p.own_world = rs->world; p.own_slabs = slabs; p.own_rot = rot;
+    OwnerMaps<true> om;
+    for (int o = 0; o < kMaxOwners; ++o) {
+      om.m[o] = tc;   // owners without rows keep a valid (never used) descriptor
+      if (o >= rs->world) continue;
+      int first = 0, last = 0;
+      b200_owner_slab_range(o, slabs, rs->world, rot, &first, &last);
+      if (last <= first) continue;
+      const long long rows = (long long)(last * 128 < a->M ? last * 128 : a->M) - (long long)first * 128;
+      B200_REQUIRE(rs->owner_base[o] != nullptr, "gemm2_rs: owner %d owns rows but has no base pointer", o);
+      rc = make_tmap_2d_sw128(&om.m[o], rs->owner_base[o], 4, a->N, (uint64_t)rows, a->ldc, 128);
+      if (rc) return rc;
+    }
+    if (bnp == 256) return launch<256, true, true, EPI_F32_ATOMIC, false, true>(ta, tb, tc, tx, p, grid, stream, om);
+    return launch<128, true, true, EPI_F32_ATOMIC, false, true>(ta, tb, tc, tx, p, grid, stream, om);
+  }
   if (epi == EPI_SWIGLU) return dispatch<256, EPI_SWIGLU>(a_mn, b_mn, ta, tb, tc, tx, p, grid, stream);
   if (bnp == 384) {
     if (epi == EPI_RESID_DROPOUT) return launch<384, false, false, EPI_RESID_DROPOUT>(ta, tb, tc, tx, p, grid, stream);

@@ -406,10 +406,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ C
 template <int BN, bool A_MN, bool B_MN, int EPI>
 static int launch(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, int grid, cudaStream_t stream) {
   auto kfn = gemm_kernel<BN, A_MN, B_MN, EPI>;
-  static bool configured = false;  // per instantiation
-  if (!configured) {
+  static bool configured[kMaxDevices] = {};   // the attribute is per device
+  if (!configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(kfn, cudaFuncAttributeMaxDynamicSharedMemorySize, SmemLayout<BN>::kTotal));
-    configured = true;
+    configured[current_device()] = true;
   }
   kfn<<<grid, 192, SmemLayout<BN>::kTotal, stream>>>(ta, tb, p);
   B200_CHECK_CUDA(cudaGetLastError());

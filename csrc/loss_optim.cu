@@ -208,10 +208,10 @@ int b200_ce_fwd_bwd(void* logits, const int64_t* labels, float* loss_sum, int ro
   B200_REQUIRE(ld % 8 == 0 && ld >= vocab, "ce: ld must be a multiple of 8 and >= vocab");
   const size_t smem = size_t(ld) * 2;
   B200_REQUIRE(smem <= 200 * 1024, "ce: a row of %d logits does not fit in shared memory", ld);
-  static size_t configured = 0;
-  if (smem > configured) {
+  static size_t configured[kMaxDevices] = {};   // the attribute is per device
+  if (smem > configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(ce_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    configured = smem;
+    configured[current_device()] = smem;
   }
   ce_fwd_bwd_kernel<<<rows, kCeThreads, smem, STREAM(stream)>>>((__nv_bfloat16*)logits, labels, loss_sum, vocab, ld,
                                                                 loss_scale, grad_scale);

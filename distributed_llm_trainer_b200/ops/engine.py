@@ -141,6 +141,9 @@ class FusedGPTEngine:
         self.end_step_hook: Optional[Callable[[], None]] = None             # DDP: join forked streams
         self.ag_hook: Optional[Callable[[int], Optional[tuple]]] = None     # FSDP: fused all-gather args for QKV
         self.hooks_capturable = False     # True when grad_ready_hook/end_step_hook only launch stream-ordered work
+        # DDP / FSDP: key ("L3.qkv", "emb", ...) -> where every rank keeps its rows of that weight gradient.  When
+        # set, the wgrad GEMMs reduce-add their tiles into the owners' buffers (GEMM -> reduce-scatter, one kernel)
+        self.rs_router: Optional[Callable[[str], Optional[tuple]]] = None
         self._bind_views()
 
     # ------------------------------------------------------------------------------------------ parameter views
@@ -185,13 +188,19 @@ class FusedGPTEngine:
         return ws
 
     # ------------------------------------------------------------------------------------------ GEMM helpers
-    def _wgrad(self, dy: torch.Tensor, x: torch.Tensor, gw: torch.Tensor) -> None:
-        """gw[N_out, K_in] (fp32) += dy[M, N_out]^T @ x[M, K_in]  -- both operands MN-major."""
+    def _wgrad(self, dy: torch.Tensor, x: torch.Tensor, gw: torch.Tensor, key: Optional[str] = None) -> None:
+        """gw[N_out, K_in] (fp32) += dy[M, N_out]^T @ x[M, K_in]  -- both operands MN-major.  With an ``rs_router``
+        the sum goes to the rows' owners instead of ``gw`` (which then only describes the layout)."""
         n_out, k_in = gw.shape
         bn = 256 if k_in % 256 == 0 else 128
         tiles = ((n_out + 127) // 128) * ((k_in + bn - 1) // bn)
         split = max(1, min(8, self.sm_count // max(tiles, 1)))
         epi = K.EPI_F32_ATOMIC
+        rs = self.rs_router(key) if (self.rs_router is not None and key is not None) else None
+        if rs is not None:
+            K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=epi, split_k=split, tile_n=bn, max_ctas=self.max_ctas,
+                   M=n_out, N=k_in, K=dy.shape[0], rs=rs)
+            return
         if self.wgrad_overwrite:
             # the destination holds exactly one contribution (FSDP per-block staging): store instead of
             # reduce-add, so the buffer needs no zero-fill; split-K still accumulates, over a zeroed matrix
@@ -257,23 +266,23 @@ class FusedGPTEngine:
         mc = self.max_ctas
         # ---- MLP branch: x_out = xmid + dropout(down(act)).  ws.dy = dropout'(ws.dx) for stream 8l+2 was
         # written by the norm backward that produced ws.dx (fused dropout_bwd_cast).
-        self._wgrad(ws.dy, a.act, G.wd)
+        self._wgrad(ws.dy, a.act, G.wd, f"L{l}.d")
         if self.fuse_swiglu_bwd:
             K.gemm(ws.dy, W.wd, ws.dgu, b_mn=True, epilogue=K.EPI_SWIGLU_BWD, aux=a.gu, half_n=I, N=I, max_ctas=mc)
         else:
             # d_act reuses the (dead by now) act buffer of this layer; SwiGLU' as a separate streaming kernel
             K.gemm(ws.dy, W.wd, ws.dact, b_mn=True, max_ctas=mc)
             K.swiglu_bwd(ws.dact, a.gu, ws.dgu)
-        self._wgrad(ws.dgu, a.xn2, G.wgu)
+        self._wgrad(ws.dgu, a.xn2, G.wgu, f"L{l}.gu")
         K.gemm(ws.dgu, W.wgu, ws.dxn, b_mn=True, max_ctas=mc)
         # ---- attention branch: xmid = x_in + dropout(o_proj(attn)); its dY comes out of the same pass
         K.rmsnorm_bwd(ws.dxn, a.xmid, W.ln2, a.rstd2, ws.dx, G.ln2, dy_next=ws.dy, p_next=cfg.dropout, rng_state=rng,
                       rng_stream=8 * l + 1)
-        self._wgrad(ws.dy, a.attn, G.wo)
+        self._wgrad(ws.dy, a.attn, G.wo, f"L{l}.o")
         K.gemm(ws.dy, W.wo, ws.dattn, b_mn=True, max_ctas=mc)
         K.attn_bwd(a.qkv, a.attn, ws.dattn, a.lse, ws.dqkv, ws.delta, ws.dq_acc, ws.B, ws.S, cfg.num_heads,
                    cfg.attention_dropout, rng, 8 * l, rope_cos=self.rope_cos, rope_sin=self.rope_sin)
-        self._wgrad(ws.dqkv, a.xn1, G.wqkv)
+        self._wgrad(ws.dqkv, a.xn1, G.wqkv, f"L{l}.qkv")
         K.gemm(ws.dqkv, W.wqkv, ws.dxn, b_mn=True, max_ctas=mc)
         if l > 0:   # ... and the dY of the previous block's MLP branch
             K.rmsnorm_bwd(ws.dxn, x_in, W.ln1, a.rstd1, ws.dx, G.ln1, dy_next=ws.dy, p_next=cfg.dropout, rng_state=rng,
@@ -307,7 +316,8 @@ class FusedGPTEngine:
                 K.gemm(logits, w, ws.dxnf32[r0:r1], b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split, tile_n=256,
                        max_ctas=self.max_ctas, K=V)
                 K.gemm(logits, ws.xnf[r0:r1], self.g_emb, a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, tile_n=256,
-                       max_ctas=self.max_ctas, M=V, K=r1 - r0)
+                       max_ctas=self.max_ctas, M=V, K=r1 - r0,
+                       rs=self.rs_router("emb") if self.rs_router is not None else None)
         if with_grad:
             K.cast_f32_bf16(ws.dxnf32, ws.dxnf)
 
@@ -344,9 +354,16 @@ class FusedGPTEngine:
                 self.release_hook(l, "backward")
             if self.grad_ready_hook is not None:
                 self.grad_ready_hook(1 + l)
-        K.embed_bwd(ws.ids, ws.dx, self.g_emb)
+        self._embed_bwd(ws)
         if self.grad_ready_hook is not None:
             self.grad_ready_hook(0)
+
+    def _embed_bwd(self, ws: _Workspace) -> None:
+        rs = self.rs_router("emb") if self.rs_router is not None else None
+        if rs is not None:
+            K.embed_bwd_rs(ws.ids, ws.dx, rs, self.vocab)
+        else:
+            K.embed_bwd(ws.ids, ws.dx, self.g_emb)
 
     def _step_body(self, ws: _Workspace, loss_scale: float) -> None:
         ws.loss_sum.zero_()

@@ -45,8 +45,25 @@ class AgArgs(C.Structure):
     ]
 
 
+class RsArgs(C.Structure):
+    """``b200_rs_args``: where every rank keeps its rows of a weight gradient (GEMM -> reduce-scatter)."""
+    _fields_ = [("owner_base", C.c_void_p), ("world", C.c_int), ("rot", C.c_int)]
+
+
+def make_rs_args(owner_base_ptrs, rot: int):
+    """(RsArgs, keep-alive pointer array) for ``gemm(..., rs=...)`` / ``embed_bwd_rs``; ``None`` entries = owners
+    without rows."""
+    arr = (C.c_void_p * len(owner_base_ptrs))(*[p if p else None for p in owner_base_ptrs])
+    return RsArgs(owner_base=C.cast(arr, C.c_void_p), world=len(owner_base_ptrs), rot=rot), arr
+
+
 _P, _I, _F, _LL, _U = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint
 _SIGS = {
+    "b200_gemm2_rs_bf16": [C.POINTER(GemmArgs), C.POINTER(RsArgs), _P],
+    "b200_sumsq_chunks": [_P, _P, _I, _P, _F, _P],
+    "b200_adamw_chunks": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _F, _F, _F, _F, _F, _P, _I, _I, _P],
+    "b200_pull_reduce_chunks": [_P, _P, _P, _I, _I, _I, _I, _P],
+    "b200_embed_bwd_rs": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "b200_gemm2_ag_bf16": [C.POINTER(GemmArgs), C.POINTER(AgArgs), _P],
     "b200_gemm_bf16": [C.POINTER(GemmArgs), _P],
     "b200_gemm2_bf16": [C.POINTER(GemmArgs), _P],
@@ -116,7 +133,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
          rope_cos=None, rope_sin=None, seq_len: int = 0, rope_cols: int = 0,
          residual=None, dropout_p: float = 0.0, rng_state=None, rng_stream: int = 0,
          aux=None, half_n: int = 0, M: Optional[int] = None, N: Optional[int] = None, K: Optional[int] = None,
-         pair: Optional[bool] = None, ag=None) -> None:
+         pair: Optional[bool] = None, ag=None, rs=None) -> None:
     """``c = a @ b`` on tcgen05.  ``pair=True`` selects the CTA-pair kernel (``cta_group::2``, 256x256 tiles,
     TMA-store epilogue); ``None`` lets ``use_pair_kernel`` decide for the epilogues that kernel implements.
 
@@ -147,6 +164,11 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
                         gather_pairs=gather_pairs)
         _call("b200_gemm2_ag_bf16", C.byref(args), C.byref(agargs), _stream())
         return
+    if rs is not None:
+        # reduce-scatter fused into the GEMM: ``rs`` = (RsArgs, keep-alive) from make_rs_args; ``c`` is only a layout
+        # template (leading dimension) -- every 128-row slab of the result is reduce-added into its owner's buffer
+        _call("b200_gemm2_rs_bf16", C.byref(args), C.byref(rs[0]), _stream())
+        return
     if pair is None:
         pair = (use_pair_kernel and M >= 256 and N >= 128 and not (a_mn and epilogue > EPI_F32_ATOMIC)
                 and not (epilogue == EPI_SWIGLU and (half_n % 128 or b_mn)))
@@ -164,6 +186,13 @@ def embed_bwd(ids, dx_f32, dweight_f32):
     rows = ids.numel()
     _call("b200_embed_bwd", ids.data_ptr(), dx_f32.data_ptr(), dweight_f32.data_ptr(), rows, dweight_f32.shape[1],
           dweight_f32.shape[0], _stream())
+
+
+def embed_bwd_rs(ids, dx_f32, rs, vocab: int):
+    """``embed_bwd`` whose destination rows live with their owners (``rs`` from make_rs_args over ``vocab`` rows)."""
+    rows, hidden = dx_f32.shape
+    _call("b200_embed_bwd_rs", ids.data_ptr(), dx_f32.data_ptr(), rs[0].owner_base, rows, hidden, vocab, rs[0].world,
+          rs[0].rot, _stream())
 
 
 def rmsnorm_fwd(x_f32, w_bf16, y_bf16, rstd, eps: float):
@@ -301,6 +330,45 @@ def adamw_bcast(master, grad, exp_avg, exp_avg_sq, shadow_ptrs, rank, world, dec
 def allreduce_scalars(pad_ptrs, rank, world, epoch_counter, inp, out, n):
     _call("b200_allreduce_scalars", pad_ptrs, rank, world, epoch_counter.data_ptr(), inp.data_ptr(), out.data_ptr(), n,
           _stream())
+
+
+CHUNK_ELEMS = 4096
+
+
+def make_chunk_table(runs, device) -> "tuple[torch.Tensor, int]":
+    """Device table of ``b200_chunk`` from runs ``(g, pg, mv, sh, n, dst)`` (element offsets; n % 4 == 0), each split
+    into pieces of at most CHUNK_ELEMS elements.  Returns (uint8 tensor holding the table, number of chunks)."""
+    import numpy as np
+
+    dt = np.dtype([("g", "<i8"), ("pg", "<i8"), ("mv", "<i8"), ("sh", "<i8"), ("n", "<i4"), ("dst", "<i4")])
+    assert dt.itemsize == 40
+    rows = []
+    for g, pg, mv, sh, n, dst in runs:
+        assert n % 4 == 0, "chunk runs must be multiples of 4 elements"
+        o = 0
+        while o < n:
+            m = min(CHUNK_ELEMS, n - o)
+            rows.append((g + o, pg + o, mv + o, sh + o, m, dst))
+            o += m
+    arr = np.array(rows, dtype=dt) if rows else np.zeros(0, dtype=dt)
+    t = torch.from_numpy(arr.view(np.uint8).copy()) if rows else torch.zeros(0, dtype=torch.uint8)
+    return t.to(device), len(rows)
+
+
+def sumsq_chunks(grad_f32, table, n_chunks, out, sq_scale: float = 1.0):
+    _call("b200_sumsq_chunks", grad_f32.data_ptr(), table.data_ptr(), n_chunks, out.data_ptr(), sq_scale, _stream())
+
+
+def adamw_chunks(master, grad, exp_avg, exp_avg_sq, param_ptrs, rank, world, decay_chunks, table, n_chunks, step, lr,
+                 beta1, beta2, eps, wd, grad_scale, zero_grad: bool = True, max_ctas: int = 0):
+    _call("b200_adamw_chunks", master.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), param_ptrs,
+          rank, world, decay_chunks.data_ptr(), table.data_ptr(), n_chunks, step, lr, beta1, beta2, eps, wd,
+          _ptr(grad_scale), int(zero_grad), max_ctas, _stream())
+
+
+def pull_reduce_chunks(src_ptrs, dst_f32, table, n_chunks, rank, world, zero_remote: bool = True):
+    _call("b200_pull_reduce_chunks", src_ptrs, dst_f32.data_ptr(), table.data_ptr(), n_chunks, rank, world,
+          int(zero_remote), _stream())
 
 
 def memcpy_async(dst_ptr: int, src_ptr: int, nbytes: int) -> None:

@@ -74,10 +74,14 @@ class SymmetricBuffer:
         return K.ptr_array([p + byte_offset for p in self.raw_ptrs])
 
     def close(self) -> None:
+        """Collective: every rank unmaps its peers' allocations, then (after a barrier) frees its own."""
         lib = _lib.lib()
+        torch.cuda.synchronize()
         for p in self._opened:
             lib.b200_ipc_close(C.c_void_p(p))
         self._opened = []
+        if dist.is_initialized() and self.world > 1:
+            dist.barrier(group=self.group)
         if self._own_ptr:
             lib.b200_device_free(C.c_void_p(self._own_ptr))
             self._own_ptr = 0

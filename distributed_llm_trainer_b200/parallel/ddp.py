@@ -4,15 +4,16 @@ Two implementations of what the reference gets from ``torch.nn.parallel.Distribu
 (ddp_trainer.py:167-172, ``no_sync`` :329-332):
 
 ``NVLinkGradSync`` (CUDA / bf16 engine path)
-    Gradients live in a flat fp32 buffer in peer-mapped memory.  After the last micro-step each rank
-    *reduces only its 1/N slice of every unit* by loading the peers' gradients straight over NVLink
-    (``b200_reduce_scatter_f32``, squared-norm partial folded in), the N partial norms are summed
-    through the signal pads, and one fused kernel applies the clip coefficient + AdamW to the slice
-    and stores the updated bf16 parameters into **every** rank's shadow buffer
-    (``b200_adamw_bcast``).  That is the DDP all-reduce + ``clip_grad_norm_`` + ``optimizer.step()``
-    of the reference in two passes over 1/N of the data, moving 4 B/param in and 2 B/param out per
-    rank instead of 2 x 4 B/param, with optimizer state sharded (ZeRO-1) for free.  Numerically it is
-    the same update on every rank (fp32 sum in a fixed rank order, so all replicas stay bit-identical).
+    Gradients live in flat fp32 buffers in peer-mapped memory and every weight matrix is owned by ranks
+    in 128-row slabs (``parallel/ownership.py``).  The wgrad GEMMs deliver their tiles to the owners
+    themselves -- a TMA reduce-add over NVLink from the epilogue (``b200_gemm2_rs_bf16``) -- so when the
+    last backward finishes the reduce-scatter has already happened, tile by tile, under the GEMM main
+    loops.  The step that follows is a barrier, the squared norm of the owned rows, a scalar all-reduce
+    through the signal pads and one AdamW launch whose bf16 result is stored into **every** rank's
+    compute copy (``b200_adamw_chunks``): the DDP all-reduce + ``clip_grad_norm_`` +
+    ``optimizer.step()`` of the reference with 4 B/param of gradient out (hidden) and 2 B/param of
+    parameters out per rank, optimizer work and state / N (ZeRO-1), and replicas that stay bit-identical
+    because every rank receives the same bf16 values from the one owner that computed them.
 
 ``BucketedDDP`` (PyTorch path: CPU/gloo tests, fp32/fp16 runs)
     Our own bucketed all-reduce: per-unit flat buckets filled by post-accumulate-grad hooks in
@@ -108,97 +109,68 @@ def shard_ranges(units, world: int) -> List[List[Tuple[int, int]]]:
 
 
 class NVLinkGradSync:
+    """Gradient synchronisation + sharded optimizer of the b200 DDP path.
+
+    The gradient all-reduce of the reference (DDP buckets fired from backward, ddp_trainer.py:329-342) does not
+    exist as a separate step here: every wgrad GEMM (and the embedding scatter) of every micro-step reduce-adds
+    its 128-row output slabs straight into the buffer of the rank that OWNS those rows
+    (``b200_gemm2_rs_bf16``: TMA reduce-add over NVLink from the GEMM's epilogue, under the main loop of the
+    next tiles).  When the last backward is done each rank already holds the cross-rank sum of its rows, and
+    the step is: barrier -> (owners pull the few norm-weight gradients) -> squared norm of the owned rows ->
+    scalar all-reduce -> clip coefficient -> ONE AdamW launch over the owned rows that stores the new bf16
+    parameters into every rank's compute copy and clears the gradient -> barrier.
+    """
+
     def __init__(self, engine, rank: int, world: int, grad_buf, shadow_buf, pads):
+        from ..ops import kernels as K
+        from .ownership import OwnershipPlan
+
         self.engine = engine
         self.store: FlatParamStore = engine.store
         self.rank, self.world = rank, world
         self.grad_buf, self.shadow_buf, self.pads = grad_buf, shadow_buf, pads
-        self.all_ranges = shard_ranges(self.store.units, world)
+        self.plan = OwnershipPlan(self.store.slots, world)
+        self.all_ranges = self.plan.all_ranges()
         self.ranges = self.all_ranges[rank]
         dev = self.store.device
         self.sumsq = torch.zeros(8, dtype=torch.float32, device=dev)
         self.sumsq_total = torch.zeros(8, dtype=torch.float32, device=dev)
         self.optimizer = None
-        self.comm_stream = torch.cuda.Stream(device=dev)
         self.max_ctas = 0
-        # B200_DDP_OVERLAP=1 forks per-unit reductions under the last backward (captured in the CUDA graph of
-        # that micro-step).  Default off: measured on 2xB200 with the small model the whole reduction is ~0.5 ms
-        # of a 52 ms step, and running it under the backward GEMMs costs them more (52.8 ms with overlap and 32
-        # comm CTAs, 62.4 ms with 4, vs 51.7 ms reducing after the backward) -- profiles/ddp_overlap_ab.md.
-        self.overlap = os.environ.get("B200_DDP_OVERLAP", "0") == "1"
-        # small grid: shares the SMs with the backward GEMMs it overlaps
-        self.comm_ctas = int(os.environ.get("B200_DDP_COMM_CTAS", "32"))
-        # B200_DDP_CE=1: peers' copies of the owned slice come over by copy engine into local scratch and the
-        # reduction kernel reads local memory only (no SM time spent waiting on NVLink loads)
-        self.ce = os.environ.get("B200_DDP_CE", "0") == "1"
-        self._ce_tmp: Optional[List[torch.Tensor]] = None
-        self._last = False
-        self._overlapped = False
-        self._units_done = 0
-
-    def _reduce_range(self, lo: int, hi: int, ctas: int) -> None:
-        """store.grad[lo:hi] = mean over ranks of their grad[lo:hi]; adds the slice's squared norm to sumsq[0]."""
-        from ..ops import kernels as K
-
-        if hi <= lo:
-            return
-        ptrs = self.grad_buf.ptrs
-        if self.ce and self.world > 1:
-            if self._ce_tmp is None:
-                mx = max(b - a for a, b in self.ranges)
-                self._ce_tmp = [torch.empty(mx, dtype=torch.float32, device=self.store.device)
-                                for _ in range(self.world - 1)]
-            tab, k = [], 0
-            for r in range(self.world):
-                if r == self.rank:
-                    tab.append(self.grad_buf.raw_ptrs[r])
-                else:
-                    t = self._ce_tmp[k]
-                    k += 1
-                    K.memcpy_async(t.data_ptr(), self.grad_buf.raw_ptrs[r] + 4 * lo, 4 * (hi - lo))
-                    tab.append(t.data_ptr() - 4 * lo)          # the kernel indexes every source at [lo, hi)
-            ptrs = K.ptr_array(tab)
-        K.reduce_scatter_f32(ptrs, self.store.grad, lo, hi, 1.0 / self.world, self.sumsq[0:1], self.rank, self.world,
-                             ctas)
+        # key -> (RsArgs, keep-alive): base pointer of every owner's rows inside its (peer-mapped) gradient buffer
+        self._rs: Dict[str, tuple] = {}
+        for key, g in self.plan.groups.items():
+            bases = []
+            for o in range(world):
+                a, b = g.row_range(o, world)
+                bases.append(grad_buf.raw_ptrs[o] + 4 * (g.offset + a * g.cols) if b > a else None)
+            self._rs[key] = K.make_rs_args(bases, g.rot)
+        engine.rs_router = self._rs.get
+        self._chunks = None
 
     def owned_ranges(self) -> List[Tuple[int, int]]:
         return self.ranges
 
+    def close(self) -> None:
+        """Collective: release the peer-mapped buffers (the engine and its store must not be used afterwards)."""
+        self.engine.rs_router = None
+        for b in (self.grad_buf, self.shadow_buf, self.pads.buf):
+            b.close()
+
     def attach_optimizer(self, opt) -> None:
-        self.optimizer = opt
-
-    def begin_micro_step(self, last: bool) -> None:
-        """Before each micro-step.  On the last one (the only one whose gradients are final -- the
-        ``no_sync`` rule of the reference, ddp_trainer.py:329-332) the engine reports every unit as soon as
-        its backward is done, and that unit's slice reduction is forked onto the comm stream so it overlaps
-        the rest of the backward pass (reference: DDP bucket hooks)."""
-        self._last = last
-        self._overlapped = False
-        if last and self.overlap:
-            self.sumsq.zero_()
-            self._units_done = 0
-            self.engine.grad_ready_hook = self._on_unit_ready
-            self.engine.end_step_hook = self._join_comm
-            self.engine.hooks_capturable = True
-            self._overlapped = True
-
-    def _on_unit_ready(self, unit: int) -> None:
+        """Builds the chunk tables (they carry the optimizer-state offsets of the owned runs)."""
         from ..ops import kernels as K
 
-        cur = torch.cuda.current_stream()
-        ev = torch.cuda.Event()
-        ev.record(cur)
-        self.comm_stream.wait_event(ev)
-        lo, hi = self.ranges[unit]
-        with torch.cuda.stream(self.comm_stream):
-            self.pads.barrier()      # every rank has finished this unit's gradients
-            self._reduce_range(lo, hi, self.comm_ctas)
-        self._units_done += 1
+        self.optimizer = opt
+        dev = self.store.device
+        assert opt.ranges == [(int(a), int(b)) for a, b in self.ranges]
+        runs = [(lo, lo, off, lo, hi - lo, -1) for (lo, hi), off in zip(opt.ranges, opt.state_offsets)]
+        self._chunks = K.make_chunk_table(runs, dev)
+        small = [(lo, lo, 0, lo, hi - lo, -1) for lo, hi in self.plan.small_ranges(self.rank)]
+        self._pull_chunks = K.make_chunk_table(small, dev)
 
-    def _join_comm(self) -> None:
-        """End of the micro-step: the compute stream waits for the forked reductions (inside a CUDA graph
-        capture this is the join that closes the fork)."""
-        torch.cuda.current_stream().wait_stream(self.comm_stream)
+    def begin_micro_step(self, last: bool) -> None:
+        """Every micro-step is the same now (its wgrads land at the owners): kept for API compatibility."""
 
     # ---- the fused step --------------------------------------------------------------------------------
     def finish_and_step(self, grad_clip: float, norm_out: Optional[torch.Tensor] = None) -> None:
@@ -208,27 +180,22 @@ class NVLinkGradSync:
         g0 = opt.param_groups[0]
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
         opt.step_count += 1
-        if self._overlapped:
-            # reductions were forked under the backward and already joined by end_step_hook
-            self.engine.grad_ready_hook = None
-            self.engine.end_step_hook = None
-        else:
-            self.sumsq.zero_()
-            # every rank's backward has finished writing its gradients
-            self.pads.barrier()
-            for lo, hi in self.ranges:
-                self._reduce_range(lo, hi, self.max_ctas)
-        # global gradient norm: sum of the per-rank partials (identical summation order everywhere)
-        self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
-        K.clip_coef(self.sumsq_total, float(grad_clip), 1.0, opt.grad_scale, norm_out)
-        for (lo, hi), off in zip(self.ranges, opt.state_offsets):
-            if hi > lo:
-                K.adamw_bcast(st.master, st.grad, opt.exp_avg[off: off + hi - lo], opt.exp_avg_sq[off: off + hi - lo],
-                              self.shadow_buf.ptrs, self.rank, self.world, opt._decay, lo, hi, opt.step_count, lr, b1,
-                              b2, eps, wd, opt.grad_scale, self.max_ctas)
-        # all peers have read my gradients (safe to zero) and all shadow stores have landed
+        self.sumsq.zero_()
+        # every rank's reduce-adds (all micro-steps of this step) have landed in the owners' buffers
         self.pads.barrier()
-        st.grad.zero_()
+        table, n = self._pull_chunks
+        K.pull_reduce_chunks(self.grad_buf.ptrs, st.grad, table, n, self.rank, self.world, zero_remote=True)
+        table, n = self._chunks
+        K.sumsq_chunks(st.grad, table, n, self.sumsq[0:1], 1.0)
+        # global gradient norm: sum of the per-rank partials (identical summation order everywhere); the buffers
+        # hold SUMS over ranks, the 1/world of the mean is folded into the clip coefficient
+        self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
+        K.clip_coef(self.sumsq_total, float(grad_clip), 1.0 / self.world, opt.grad_scale, norm_out)
+        K.adamw_chunks(st.master, st.grad, opt.exp_avg, opt.exp_avg_sq, self.shadow_buf.ptrs, self.rank, self.world,
+                       opt._decay, table, n, opt.step_count, lr, b1, b2, eps, wd, opt.grad_scale, zero_grad=True,
+                       max_ctas=self.max_ctas)
+        # all parameter stores have landed and every owned gradient is zero again: the next step may start
+        self.pads.barrier()
 
     # ---- checkpoint support (cold path, NCCL) ----------------------------------------------------------------
     def _gather_flat(self, local_pieces: List[torch.Tensor], out_full: torch.Tensor) -> None:
@@ -287,11 +254,7 @@ def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, s
     store.refresh_shadow()
     eng = FusedGPTEngine(model, store=store, seed=seed)
     sync = NVLinkGradSync(eng, rank, world_size, grad_buf, shadow_buf, pads)
-    # first launches of the comm kernels happen here, eagerly, not inside a later CUDA-graph capture
-    from ..ops import kernels as K
-
-    pads.barrier()
-    K.reduce_scatter_f32(grad_buf.ptrs, store.grad, 0, 128, 1.0, sync.sumsq[0:1], rank, world_size, 1)
+    # first launch of the pad kernels happens here, eagerly, not inside a later CUDA-graph capture
     pads.barrier()
     torch.cuda.synchronize()
     dist.barrier()

@@ -295,6 +295,7 @@ class ShardedGPT:
         e.fuse_swiglu_bwd = True
         e.end_step_hook = None
         e.hooks_capturable = False
+        e.rs_router = None
         e.max_ctas = 0
         e.wgrad_overwrite = not self.accum_local    # rotating staging buffers hold one contribution per use
         e.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count

@@ -274,6 +274,11 @@ class FSDPTrainer:
                 del sh._host                      # host master shard is rebuilt from the loaded weights
             self.opt_state["step"] = full.step_count
             opt.step_count = full.step_count
+            # hyper-parameters travel with the checkpoint too (lr is written AFTER each step, so the first step
+            # after a resume must run at the saved value, not at the peak rate the facade was built with)
+            for g, src in zip(opt.param_groups, full.param_groups):
+                for k in ("lr", "betas", "eps", "weight_decay"):
+                    g[k] = src[k]
             del full
             sh.release_full_master()
         else:

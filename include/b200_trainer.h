@@ -100,6 +100,28 @@ typedef struct b200_ag_args {
 } b200_ag_args;
 int b200_gemm2_ag_bf16(const b200_gemm_args* args, const b200_ag_args* ag, void* stream);
 
+/* Reduce-scatter fused into the producing GEMM (the gradient path of DDP and FSDP; reference: DDP's bucketed
+ * all-reduce fired from backward, ddp_trainer.py:329-342, and FSDP's reduce_scatter_tensor, fsdp_trainer.py:383).
+ * C = A*B is a weight gradient (wgrad form: MN-major A and B, B200_EPI_F32_ATOMIC) whose rows are owned by
+ * ranks in 128-row slabs: slab s of `slabs = ceil(M/128)` belongs to rank ((s*world)/slabs + rot) % world, so
+ * every rank owns one contiguous run of slabs.  Each CTA's 128-row output slab is reduce-added by TMA
+ * (cp.reduce.async.bulk.tensor .add) straight into its OWNER's fp32 buffer -- peer memory over NVLink unless
+ * the owner is the calling rank -- from the same swizzled staging ring the local epilogue uses, so the
+ * transfer rides under the main loop of the following tiles.  After every rank has run its GEMM (and a
+ * barrier), owner o holds sum_r C_r for its rows: there is no separate reduce-scatter kernel.
+ *   owner_base[o]: device pointer (mapped into this process) to the first row rank o owns, row pitch args->ldc;
+ *                  NULL allowed for ranks that own no slab.  args->C is ignored (may be NULL). */
+typedef struct b200_rs_args {
+  const void* const* owner_base; /* host array [world] */
+  int world;                     /* 1..8 */
+  int rot;                       /* rotation of the owner assignment (spreads short tensors over the ranks) */
+} b200_rs_args;
+int b200_gemm2_rs_bf16(const b200_gemm_args* args, const b200_rs_args* rs, void* stream);
+/* The ownership rule above, for callers that lay out the owners' buffers: owner of a slab, and the slab run
+ * [first, last) of an owner (empty when first >= last).  Host-only helpers, no GPU work. */
+int b200_slab_owner(int slab, int slabs, int world, int rot);
+int b200_owner_slab_range(int owner, int slabs, int world, int rot, int* first, int* last);
+
 /* ---------------------------------------------------------------- normalisation / elementwise */
 /* Token embedding gather into the fp32 residual stream (reference gpt.py:438). ids: int64 [rows]. */
 int b200_embed_fwd(const int64_t* ids, const void* weight_bf16, float* out, int rows, int hidden, int vocab,
@@ -244,6 +266,37 @@ int b200_reduce_scatter_f32_accum(const void* const* full_grad_ptrs, float* dst_
                                   long long n, float scale, int rank, int world, int max_ctas, void* stream);
 int b200_reduce_scatter_bf16_accum(const void* const* full_grad_ptrs, float* dst_shard, long long src_offset,
                                    long long n, float scale, int rank, int world, int max_ctas, void* stream);
+
+
+/* ---- optimizer side of the fused reduce-scatter (b200_gemm2_rs_bf16): chunk tables ---------------------------
+ * A rank's owned parameters are many short runs (128-row slabs of weight matrices, whole norm vectors).  The
+ * caller flattens them into chunks of <= 4096 elements (n % 4 == 0) in a device array so that ONE launch covers
+ * them all.  Offsets are in elements:
+ *   g   global flat index of the first element (weight-decay table / source offset for pulls)
+ *   pg  offset into the local fp32 master / gradient arrays      mv  offset into the local moment arrays
+ *   sh  offset into the destination bf16 parameter buffer(s)     dst receiving rank, or -1 = every rank */
+typedef struct b200_chunk {
+  long long g, pg, mv, sh;
+  int n, dst;
+} b200_chunk;
+/* out[0] += sq_scale * sum(grad[chunks]^2)   (reference: clip_grad_norm_, ddp_trainer.py:350, fsdp_trainer.py:388) */
+int b200_sumsq_chunks(const float* grad, const b200_chunk* chunks_dev, int n_chunks, float* out, float sq_scale,
+                      void* stream);
+/* AdamW over the chunks; updated bf16 parameters are stored into rank dst's buffer (param_ptrs[dst] + sh) or into
+ * every rank's (dst = -1); zero_grad != 0 clears the gradient in the same pass (reference: optimizer.step +
+ * zero_grad + the parameter half of the all-reduce / next all-gather, ddp_trainer.py:356, fsdp_trainer.py:391). */
+int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg_sq, const void* const* param_ptrs,
+                      int rank, int world, const uint8_t* decay_chunks, const b200_chunk* chunks_dev, int n_chunks,
+                      int step, float lr, float beta1, float beta2, float eps, float weight_decay,
+                      const float* grad_scale, int zero_grad, int max_ctas, void* stream);
+/* dst[pg ..] = sum_r src_r[g ..] over the chunks (small tensors that every rank accumulates locally);
+ * zero_remote != 0 also clears the peers' copies for the next step. */
+int b200_pull_reduce_chunks(const void* const* src_ptrs, float* dst, const b200_chunk* chunks_dev, int n_chunks,
+                            int rank, int world, int zero_remote, void* stream);
+/* b200_embed_bwd with owner-directed rows (same slab rule as b200_gemm2_rs_bf16 over `vocab` rows): owner_base[o]
+ * points at the first embedding-gradient row rank o owns. */
+int b200_embed_bwd_rs(const int64_t* ids, const float* dx, const void* const* owner_base, int rows, int hidden,
+                      int vocab, int world, int rot, void* stream);
 
 #ifdef __cplusplus
 }

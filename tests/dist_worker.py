@@ -304,17 +304,75 @@ def mode_aggemm(tmp):
     pads.buf.close()
 
 
+def mode_rsgemm(tmp):
+    """GEMM -> reduce-scatter over real NVLink peers: every rank runs the same wgrad GEMM on its own data and the
+    128-row slabs of the result are reduce-added into their owners' buffers; after a barrier each owner must hold
+    the all-reduced rows.  Same for the owner-directed embedding scatter."""
+    from distributed_llm_trainer_b200.ops import kernels as K
+    from distributed_llm_trainer_b200.parallel.comm import SignalPads, SymmetricBuffer, wrap_pointer
+    from distributed_llm_trainer_b200.parallel.ownership import SlabGroup
+
+    local = int(os.environ["LOCAL_RANK"])
+    dev = torch.device(f"cuda:{local}")
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    pads = SignalPads(dev)
+    for n_out, k_in, T, rot in ((2304, 768, 2048, 0), (768, 768, 1024, 1), (1000, 256, 512, 3)):
+        g = SlabGroup("t", 0, n_out, k_in, rot % world, ("t",))
+        buf = SymmetricBuffer(n_out * k_in, torch.float32, dev)       # full-size layout, owned rows in place
+        bases = []
+        for o in range(world):
+            a, b = g.row_range(o, world)
+            bases.append(buf.raw_ptrs[o] + 4 * a * k_in if b > a else None)
+        rs = K.make_rs_args(bases, g.rot)
+        torch.manual_seed(77 + rank)
+        dy = (torch.randn(T, n_out, device=dev) * 0.3).to(torch.bfloat16)
+        x = (torch.randn(T, k_in, device=dev) * 0.3).to(torch.bfloat16)
+        want = dy.float().t() @ x.float()
+        dist.all_reduce(want)
+        pads.barrier()
+        for rep in (1, 2):
+            K.gemm(dy, x, buf.local.view(n_out, k_in), a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=rep,
+                   tile_n=256 if k_in % 256 == 0 else 128, M=n_out, N=k_in, K=T, rs=rs)
+            pads.barrier()
+            torch.cuda.synchronize()
+            a, b = g.row_range(rank, world)
+            if b > a:
+                got = buf.local.view(n_out, k_in)[a:b]
+                err = ((got - rep * want[a:b]).norm() / (rep * want[a:b]).norm()).item()
+                assert err < 2e-3, f"gemm_rs {n_out}x{k_in} rep {rep}: rel L2 {err:.3e}"
+            mine = torch.zeros(n_out, dtype=torch.bool, device=dev)
+            mine[a:b] = True
+            assert torch.all(buf.local.view(n_out, k_in)[~mine] == 0), "rows this rank does not own were written"
+        # embedding scatter into the same owners
+        buf.local.zero_()
+        pads.barrier()
+        ids = torch.randint(0, n_out, (4096,), device=dev)
+        dx = torch.randn(4096, k_in, device=dev)
+        ref = torch.zeros(n_out, k_in, device=dev)
+        ref.index_add_(0, ids, dx)
+        dist.all_reduce(ref)
+        K.embed_bwd_rs(ids, dx, rs, n_out)
+        pads.barrier()
+        torch.cuda.synchronize()
+        a, b = g.row_range(rank, world)
+        if b > a:
+            close(buf.local.view(n_out, k_in)[a:b], ref[a:b], 1e-4, "embed_bwd_rs")
+        dist.barrier()
+        buf.close()
+    pads.buf.close()
+
+
 def main():
     mode = sys.argv[1]
     tmp = sys.argv[2] if len(sys.argv) > 2 else "/tmp/b200_dist_test"
     os.makedirs(tmp, exist_ok=True)
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
-    if mode in ("ddp", "ddp:overlap", "ddp:ce", "ddp:overlapce"):
-        if "overlap" in mode:
-            os.environ["B200_DDP_OVERLAP"] = "1"    # fork the per-unit reductions under the last backward
-        if mode.endswith("ce"):
-            os.environ["B200_DDP_CE"] = "1"         # peers' slices by copy engine, local reduction kernel
+    if mode == "ddp":
         mode_ddp(tmp)
+    elif mode == "rsgemm":
+        mode_rsgemm(tmp)
     elif mode.startswith("fsdp"):
         parts = mode.split(":")
         opt = parts[2] if len(parts) > 2 else ""

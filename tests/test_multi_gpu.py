@@ -24,10 +24,9 @@ def _torchrun(mode, tmp, nproc, port):
 
 @pytest.mark.parametrize("mode,port", [("comm", 29711), ("ddp", 29712), ("fsdp:FULL_SHARD", 29713),
                                        ("fsdp:SHARD_GRAD_OP", 29714), ("fsdp:NO_SHARD", 29715),
-                                       ("fsdp:FULL_SHARD:offload", 29716), ("ddp:overlap", 29717), ("aggemm", 29718),
+                                       ("fsdp:FULL_SHARD:offload", 29716), ("rsgemm", 29717), ("aggemm", 29718),
                                        ("fsdp:FULL_SHARD:fuseag", 29719), ("fsdp:FULL_SHARD:smgather", 29720),
-                                       ("fsdp:FULL_SHARD:everymicro", 29721), ("ddp:ce", 29722),
-                                       ("ddp:overlapce", 29723)])
+                                       ("fsdp:FULL_SHARD:everymicro", 29721)])
 def test_multi_gpu(mode, port, tmp_path):
     n = _ngpu()
     if n < 2:
