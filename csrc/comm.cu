@@ -367,7 +367,7 @@ adamw_chunks_kernel(float* __restrict__ master, float* __restrict__ grad, float*
 }
 
 // Small tensors (norm weights) accumulate in every rank's own buffer; their owner pulls the peers' copies:
-// dst[pg ..] = sum_r src_r[g ..], and the peers' copies are cleared remotely for the next step (zero_remote).
+// dst[pg ..] = sum_r src_r[g ..], and every rank's copy is cleared for the next step (zero_remote).
 __global__ void __launch_bounds__(256)
 pull_reduce_chunks_kernel(PeerTable srcs, float* __restrict__ dst, const Chunk* __restrict__ ch, int nch, int rank,
                           int world, int zero_remote) {
@@ -380,9 +380,9 @@ pull_reduce_chunks_kernel(PeerTable srcs, float* __restrict__ dst, const Chunk* 
         float* src = reinterpret_cast<float*>(srcs.p[(rank + r) % world]) + k.g + e;
         const float4 a = ld_peer_f4(src);
         s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
-        if (zero_remote && r != 0) *reinterpret_cast<float4*>(src) = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (zero_remote) *reinterpret_cast<float4*>(src) = make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      *reinterpret_cast<float4*>(dst + k.pg + e) = s;
+      *reinterpret_cast<float4*>(dst + k.pg + e) = s;   // last: dst may be this rank's own source
     }
   }
 }

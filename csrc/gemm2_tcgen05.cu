@@ -81,6 +81,7 @@ struct Params {
   int ag_rank, ag_world;
   // ---- reduce-scatter fused into the epilogue (OWN instantiations): C's 128-row slabs belong to ranks ---------
   int own_world, own_slabs, own_rot;   // owner of slab s = ((s * world) / slabs + rot) % world
+  int own_prev;                        // tma_x = this rank's own accumulator: owner += acc + prev
 };
 
 // One output tensor map per owner (OWN instantiations): map o covers the rows of C that rank o owns, at their
@@ -422,6 +423,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         }
       }
     }
+    if constexpr (OWN) {
+      if (p.own_prev && epi_leader) {   // locally accumulated gradient: prefetch runs two units ahead
+        for (long u = 0; u < 2 && u < total_units; ++u) {
+          int m0, n0, c;
+          unit_coords(u, m0, n0, c);
+          mbar_expect_tx(&ld_bar[u % NB], kEpiBuf);
+          tma_load_2d(smem_epi + (u % NB) * kEpiBuf, &tma_x, &ld_bar[u % NB], n0 + c * 32, m0);
+        }
+      }
+    }
     if constexpr (EPI == EPI_SWIGLU_BWD) {
       if (epi_leader && total_units > 0) {   // [gate|up] prefetch runs one unit (a pair of slots) ahead
         int m0, n0, c;
@@ -499,36 +510,78 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
           stage_end(&tma_c, n0 + c * 64, m0, false);
         }
       } else if constexpr (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC) {
+        if constexpr (OWN) {
+          // GEMM -> reduce-scatter in one kernel: this CTA's 128 rows are one slab of C; its owner's map (peer
+          // memory over NVLink unless the owner is this rank) takes the reduce-add.  Rows beyond M belong to
+          // nobody (the per-owner maps clip the last slab).  With own_prev the locally accumulated gradient of the
+          // earlier micro-steps (tma_x) is prefetched into the staging slot and travels in the same reduce-add:
+          // owner += acc + prev (added by the first K split only).
+          const bool own_valid = m0 < p.M;
+          const int own_s = m0 >> 7;
+          const int own_op = own_valid ? (own_s * p.own_world) / p.own_slabs : 0;   // owner before rotation
+          int own_o = own_op + p.own_rot;
+          if (own_o >= p.own_world) own_o -= p.own_world;
+          const int own_row = m0 - (((own_op * p.own_slabs + p.own_world - 1) / p.own_world) << 7);
+          const bool add_prev = p.own_prev != 0 && t < tiles_mn;                    // K split 0
 #pragma unroll 1
-        for (int c = 0; c < kUnits; ++c) {
-          const uint32_t slot = stage_begin();
-          uint32_t v[16];
-          tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
-          tmem_ld_wait();
-          if (c == kUnits - 1) release_tmem(buf);
-          const uint32_t row_addr = slot + r_in * 128;
+          for (int c = 0; c < kUnits; ++c, ++u_glob) {
+            uint32_t slot;
+            if (p.own_prev) {
+              if (epi_leader) {   // prev prefetch two units ahead; that slot was last read by the reduce of unit u-2
+                tma_store_wait_read<1>();
+                const long un = u_glob + 2;
+                if (un < total_units) {
+                  int pm0, pn0, pc;
+                  unit_coords(un, pm0, pn0, pc);
+                  mbar_expect_tx(&ld_bar[un % NB], kEpiBuf);
+                  tma_load_2d(smem_epi + (un % NB) * kEpiBuf, &tma_x, &ld_bar[un % NB], pn0 + pc * 32, pm0);
+                }
+              }
+              slot = epi_base + uint32_t(u_glob % NB) * kEpiBuf;
+            } else {
+              slot = stage_begin();
+            }
+            uint32_t v[16];
+            tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
+            tmem_ld_wait();
+            if (c == kUnits - 1) release_tmem(buf);
+            const uint32_t row_addr = slot + r_in * 128;
+            if (p.own_prev) mbar_wait(&ld_bar[u_glob % NB], uint32_t(u_glob / NB) & 1);
 #pragma unroll
-          for (int cc = 0; cc < 4; ++cc)
-            st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
-          if constexpr (OWN) {
-            // GEMM -> reduce-scatter in one kernel: this CTA's 128 rows are one slab of C; its owner's map
-            // (peer memory over NVLink unless the owner is this rank) takes the reduce-add.  Rows beyond M
-            // belong to nobody (the per-owner maps clip the last slab).
+            for (int cc = 0; cc < 4; ++cc) {
+              const uint32_t addr = row_addr + (((hf * 4 + cc) ^ sw) << 4);
+              if (add_prev) {
+                const uint4 q4 = ld_shared_v4(addr);
+                st_shared_v4_u32(addr, __float_as_uint(__uint_as_float(q4.x) + __uint_as_float(v[cc * 4 + 0])),
+                                 __float_as_uint(__uint_as_float(q4.y) + __uint_as_float(v[cc * 4 + 1])),
+                                 __float_as_uint(__uint_as_float(q4.z) + __uint_as_float(v[cc * 4 + 2])),
+                                 __float_as_uint(__uint_as_float(q4.w) + __uint_as_float(v[cc * 4 + 3])));
+              } else {
+                st_shared_v4_u32(addr, v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
+              }
+            }
             fence_proxy_async_smem();
             named_bar_sync(1, kEpiThreads);
             if (epi_leader) {
-              if (m0 < p.M) {
-                const int s = m0 >> 7;
-                const int op = (s * p.own_world) / p.own_slabs;             // owner before rotation
-                int o = op + p.own_rot;
-                if (o >= p.own_world) o -= p.own_world;
-                const int first = (op * p.own_slabs + p.own_world - 1) / p.own_world;   // its first slab
-                tma_reduce_add_2d(&om.m[o], smem_epi + (g % NB) * kEpiBuf, n0 + c * 32, m0 - (first << 7));
-              }
+              if (own_valid)
+                tma_reduce_add_2d(&om.m[own_o], reinterpret_cast<void*>(smem_epi + (p.own_prev ? (u_glob % NB) : (g % NB)) * kEpiBuf),
+                                  n0 + c * 32, own_row);
               tma_store_commit();   // one (possibly empty) group per unit: the slot-reuse waits count groups
             }
             ++g;
-          } else {
+          }
+        } else {
+#pragma unroll 1
+          for (int c = 0; c < kUnits; ++c) {
+            const uint32_t slot = stage_begin();
+            uint32_t v[16];
+            tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
+            tmem_ld_wait();
+            if (c == kUnits - 1) release_tmem(buf);
+            const uint32_t row_addr = slot + r_in * 128;
+#pragma unroll
+            for (int cc = 0; cc < 4; ++cc)
+              st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
             stage_end(&tma_c, n0 + c * 32, m0, EPI == EPI_F32_ATOMIC);
           }
         }
@@ -867,6 +920,11 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, const b200
     const int slabs = (a->M + 127) / 128;
     const int rot = ((rs->rot % rs->world) + rs->world) % rs->world;
     p.own_world = rs->world; p.own_slabs = slabs; p.own_rot = rot;
+    p.own_prev = rs->prev != nullptr;
+    if (rs->prev != nullptr) {
+      rc = make_tmap_2d_sw128(&tx, rs->prev, 4, a->N, a->M, a->ldc, 128);
+      if (rc) return rc;
+    }
     OwnerMaps<true> om;
     for (int o = 0; o < kMaxOwners; ++o) {
       om.m[o] = tc;   // owners without rows keep a valid (never used) descriptor

@@ -144,6 +144,10 @@ class FusedGPTEngine:
         # DDP / FSDP: key ("L3.qkv", "emb", ...) -> where every rank keeps its rows of that weight gradient.  When
         # set, the wgrad GEMMs reduce-add their tiles into the owners' buffers (GEMM -> reduce-scatter, one kernel)
         self.rs_router: Optional[Callable[[str], Optional[tuple]]] = None
+        # what a micro-step does with its weight gradients: "add" accumulates into the local fp32 buffer, "store"
+        # overwrites it (first micro-step of a step: no zero-fill needed), "rs" sends local accumulation + this
+        # micro-step's product to the owners (last micro-step under DDP / FSDP; needs rs_router)
+        self.grad_mode = "add"
         self._bind_views()
 
     # ------------------------------------------------------------------------------------------ parameter views
@@ -196,12 +200,13 @@ class FusedGPTEngine:
         tiles = ((n_out + 127) // 128) * ((k_in + bn - 1) // bn)
         split = max(1, min(8, self.sm_count // max(tiles, 1)))
         epi = K.EPI_F32_ATOMIC
-        rs = self.rs_router(key) if (self.rs_router is not None and key is not None) else None
+        rs = self._rs(key)
         if rs is not None:
-            K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=epi, split_k=split, tile_n=bn, max_ctas=self.max_ctas,
-                   M=n_out, N=k_in, K=dy.shape[0], rs=rs)
+            # every K split sends its partial product over NVLink: cap the split (traffic) at 4
+            K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=epi, split_k=min(split, 4), tile_n=bn,
+                   max_ctas=self.max_ctas, M=n_out, N=k_in, K=dy.shape[0], rs=rs)
             return
-        if self.wgrad_overwrite:
+        if self.wgrad_overwrite or self.grad_mode == "store":   # ("rs1" never gets here: it always has an owner table)
             # the destination holds exactly one contribution (FSDP per-block staging): store instead of
             # reduce-add, so the buffer needs no zero-fill; split-K still accumulates, over a zeroed matrix
             if split > 1:
@@ -210,6 +215,13 @@ class FusedGPTEngine:
                 epi = K.EPI_F32
         K.gemm(dy, x, gw, a_mn=True, b_mn=True, epilogue=epi, split_k=split, tile_n=bn,
                max_ctas=self.max_ctas, M=n_out, N=k_in, K=dy.shape[0])
+
+    def _rs(self, key: Optional[str], prev: Optional[bool] = None):
+        """Owner table for ``key`` when this micro-step delivers to the owners ("rs": with the local accumulation of
+        the earlier micro-steps; "rs1": a step of ONE micro-step, the local buffer holds nothing valid)."""
+        if self.grad_mode not in ("rs", "rs1") or self.rs_router is None or key is None:
+            return None
+        return self.rs_router(key, (self.grad_mode == "rs") if prev is None else prev)
 
     def _wave_split(self, tiles: int, k_blocks: int) -> int:
         """Split-K factor for a reduce-add GEMM of ``tiles`` 256-row pair tiles: the one whose tiles x split
@@ -315,9 +327,14 @@ class FusedGPTEngine:
                 split = self._wave_split(tiles, (V + 63) // 64)
                 K.gemm(logits, w, ws.dxnf32[r0:r1], b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split, tile_n=256,
                        max_ctas=self.max_ctas, K=V)
-                K.gemm(logits, ws.xnf[r0:r1], self.g_emb, a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, tile_n=256,
-                       max_ctas=self.max_ctas, M=V, K=r1 - r0,
-                       rs=self.rs_router("emb") if self.rs_router is not None else None)
+                # tied-embedding gradient: the first chunk of a "store" micro-step overwrites, the last chunk of an
+                # "rs" micro-step carries everything accumulated so far to the owners, the rest accumulate locally
+                first, final = r0 == 0, r1 == M
+                fresh = self.grad_mode in ("store", "rs1")       # nothing valid in the local buffer yet
+                rs = self._rs("emb", prev=(self.grad_mode == "rs" or not first)) if final else None
+                K.gemm(logits, ws.xnf[r0:r1], self.g_emb, a_mn=True, b_mn=True,
+                       epilogue=K.EPI_F32 if (first and fresh and rs is None) else K.EPI_F32_ATOMIC, tile_n=256,
+                       max_ctas=self.max_ctas, M=V, K=r1 - r0, rs=rs)
         if with_grad:
             K.cast_f32_bf16(ws.dxnf32, ws.dxnf)
 
@@ -359,7 +376,7 @@ class FusedGPTEngine:
             self.grad_ready_hook(0)
 
     def _embed_bwd(self, ws: _Workspace) -> None:
-        rs = self.rs_router("emb") if self.rs_router is not None else None
+        rs = self._rs("emb")
         if rs is not None:
             K.embed_bwd_rs(ws.ids, ws.dx, rs, self.vocab)
         else:
@@ -391,7 +408,7 @@ class FusedGPTEngine:
         # kernels onto a second stream (and joins in end_step_hook), which a captured graph records faithfully
         blocking = (self.release_hook is not None or self.weights_hook is not None
                     or (self.grad_ready_hook is not None and not self.hooks_capturable))
-        key = (float(loss_scale), self.max_ctas, self.grad_ready_hook is not None)
+        key = (float(loss_scale), self.max_ctas, self.grad_ready_hook is not None, self.grad_mode)
         if self.use_graphs and not blocking and ws.calls > 2:
             entry = ws.graphs.get(key)
             if entry is None:

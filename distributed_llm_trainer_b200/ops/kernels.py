@@ -47,14 +47,14 @@ class AgArgs(C.Structure):
 
 class RsArgs(C.Structure):
     """``b200_rs_args``: where every rank keeps its rows of a weight gradient (GEMM -> reduce-scatter)."""
-    _fields_ = [("owner_base", C.c_void_p), ("world", C.c_int), ("rot", C.c_int)]
+    _fields_ = [("owner_base", C.c_void_p), ("world", C.c_int), ("rot", C.c_int), ("prev", C.c_void_p)]
 
 
-def make_rs_args(owner_base_ptrs, rot: int):
+def make_rs_args(owner_base_ptrs, rot: int, prev_ptr: Optional[int] = None):
     """(RsArgs, keep-alive pointer array) for ``gemm(..., rs=...)`` / ``embed_bwd_rs``; ``None`` entries = owners
-    without rows."""
+    without rows.  ``prev_ptr``: this rank's own fp32 accumulator of the same matrix (sent along: owner += acc + prev)."""
     arr = (C.c_void_p * len(owner_base_ptrs))(*[p if p else None for p in owner_base_ptrs])
-    return RsArgs(owner_base=C.cast(arr, C.c_void_p), world=len(owner_base_ptrs), rot=rot), arr
+    return RsArgs(owner_base=C.cast(arr, C.c_void_p), world=len(owner_base_ptrs), rot=rot, prev=prev_ptr), arr
 
 
 _P, _I, _F, _LL, _U = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint

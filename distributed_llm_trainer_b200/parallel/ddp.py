@@ -121,14 +121,17 @@ class NVLinkGradSync:
     parameters into every rank's compute copy and clears the gradient -> barrier.
     """
 
-    def __init__(self, engine, rank: int, world: int, grad_buf, shadow_buf, pads):
+    def __init__(self, engine, rank: int, world: int, grad_buf, shadow_buf, pads, red_buf):
         from ..ops import kernels as K
         from .ownership import OwnershipPlan
 
         self.engine = engine
         self.store: FlatParamStore = engine.store
         self.rank, self.world = rank, world
-        self.grad_buf, self.shadow_buf, self.pads = grad_buf, shadow_buf, pads
+        # grad_buf: this rank's own accumulator (micro-steps before the last add into it locally; peer-mapped only so
+        # that owners can pull the few norm-weight gradients).  red_buf: where the owners' rows receive the
+        # cross-rank sums (reduce-adds from every rank's last wgrad GEMMs); read and cleared by the AdamW launch.
+        self.grad_buf, self.shadow_buf, self.pads, self.red_buf = grad_buf, shadow_buf, pads, red_buf
         self.plan = OwnershipPlan(self.store.slots, world)
         self.all_ranges = self.plan.all_ranges()
         self.ranges = self.all_ranges[rank]
@@ -138,14 +141,15 @@ class NVLinkGradSync:
         self.optimizer = None
         self.max_ctas = 0
         # key -> (RsArgs, keep-alive): base pointer of every owner's rows inside its (peer-mapped) gradient buffer
-        self._rs: Dict[str, tuple] = {}
+        self._rs: Dict[Tuple[str, bool], tuple] = {}
         for key, g in self.plan.groups.items():
             bases = []
             for o in range(world):
                 a, b = g.row_range(o, world)
-                bases.append(grad_buf.raw_ptrs[o] + 4 * (g.offset + a * g.cols) if b > a else None)
-            self._rs[key] = K.make_rs_args(bases, g.rot)
-        engine.rs_router = self._rs.get
+                bases.append(red_buf.raw_ptrs[o] + 4 * (g.offset + a * g.cols) if b > a else None)
+            self._rs[(key, False)] = K.make_rs_args(bases, g.rot)
+            self._rs[(key, True)] = K.make_rs_args(bases, g.rot, prev_ptr=grad_buf.raw_ptrs[rank] + 4 * g.offset)
+        engine.rs_router = lambda key, prev: self._rs.get((key, bool(prev)))
         self._chunks = None
 
     def owned_ranges(self) -> List[Tuple[int, int]]:
@@ -154,7 +158,7 @@ class NVLinkGradSync:
     def close(self) -> None:
         """Collective: release the peer-mapped buffers (the engine and its store must not be used afterwards)."""
         self.engine.rs_router = None
-        for b in (self.grad_buf, self.shadow_buf, self.pads.buf):
+        for b in (self.grad_buf, self.red_buf, self.shadow_buf, self.pads.buf):
             b.close()
 
     def attach_optimizer(self, opt) -> None:
@@ -169,8 +173,14 @@ class NVLinkGradSync:
         small = [(lo, lo, 0, lo, hi - lo, -1) for lo, hi in self.plan.small_ranges(self.rank)]
         self._pull_chunks = K.make_chunk_table(small, dev)
 
-    def begin_micro_step(self, last: bool) -> None:
-        """Every micro-step is the same now (its wgrads land at the owners): kept for API compatibility."""
+    def begin_micro_step(self, index: int, count: int) -> None:
+        """Micro-step ``index`` of ``count``: the first overwrites the local accumulator (no zero-fill pass), the
+        middle ones add to it, and the LAST one's wgrad GEMMs send accumulator + their own product to the owners --
+        the reference's ``no_sync()`` rule (ddp_trainer.py:329-332): gradients cross the wire once per step."""
+        if os.environ.get("B200_DDP_DEBUG_NO_RS") == "1":   # timing attribution only (wrong gradients): never leave the GPU
+            self.engine.grad_mode = "add"
+            return
+        self.engine.grad_mode = "rs1" if count == 1 else ("store" if index == 0 else ("rs" if index == count - 1 else "add"))
 
     # ---- the fused step --------------------------------------------------------------------------------
     def finish_and_step(self, grad_clip: float, norm_out: Optional[torch.Tensor] = None) -> None:
@@ -180,22 +190,31 @@ class NVLinkGradSync:
         g0 = opt.param_groups[0]
         lr, (b1, b2), eps, wd = g0["lr"], g0["betas"], g0["eps"], g0["weight_decay"]
         opt.step_count += 1
+        mark = getattr(self, "trace", None) or (lambda name: None)   # benchmarks/bench_ddp_breakdown.py: event per phase
         self.sumsq.zero_()
-        # every rank's reduce-adds (all micro-steps of this step) have landed in the owners' buffers
+        mark("start")
+        # every rank's reduce-adds (the last micro-step's wgrad GEMMs) have landed in the owners' buffers
         self.pads.barrier()
+        mark("barrier")
         table, n = self._pull_chunks
-        K.pull_reduce_chunks(self.grad_buf.ptrs, st.grad, table, n, self.rank, self.world, zero_remote=True)
+        red = self.red_buf.local
+        K.pull_reduce_chunks(self.grad_buf.ptrs, red, table, n, self.rank, self.world, zero_remote=True)
         table, n = self._chunks
-        K.sumsq_chunks(st.grad, table, n, self.sumsq[0:1], 1.0)
+        mark("pull")
+        K.sumsq_chunks(red, table, n, self.sumsq[0:1], 1.0)
+        mark("sumsq")
         # global gradient norm: sum of the per-rank partials (identical summation order everywhere); the buffers
         # hold SUMS over ranks, the 1/world of the mean is folded into the clip coefficient
         self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
         K.clip_coef(self.sumsq_total, float(grad_clip), 1.0 / self.world, opt.grad_scale, norm_out)
-        K.adamw_chunks(st.master, st.grad, opt.exp_avg, opt.exp_avg_sq, self.shadow_buf.ptrs, self.rank, self.world,
+        mark("allreduce+clip")
+        K.adamw_chunks(st.master, red, opt.exp_avg, opt.exp_avg_sq, self.shadow_buf.ptrs, self.rank, self.world,
                        opt._decay, table, n, opt.step_count, lr, b1, b2, eps, wd, opt.grad_scale, zero_grad=True,
                        max_ctas=self.max_ctas)
+        mark("adamw")
         # all parameter stores have landed and every owned gradient is zero again: the next step may start
         self.pads.barrier()
+        mark("barrier2")
 
     # ---- checkpoint support (cold path, NCCL) ----------------------------------------------------------------
     def _gather_flat(self, local_pieces: List[torch.Tensor], out_full: torch.Tensor) -> None:
@@ -246,6 +265,7 @@ def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, s
     named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
     _, _, total = plan_layout(named)
     grad_buf = SymmetricBuffer(total, torch.float32, dev)
+    red_buf = SymmetricBuffer(total, torch.float32, dev)
     shadow_buf = SymmetricBuffer(total, torch.bfloat16, dev)
     pads = SignalPads(dev)
     store = FlatParamStore(model, device=dev, grad_buffer=grad_buf.local, shadow_buffer=shadow_buf.local)
@@ -253,7 +273,7 @@ def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, s
     dist.broadcast(store.master, src=0)
     store.refresh_shadow()
     eng = FusedGPTEngine(model, store=store, seed=seed)
-    sync = NVLinkGradSync(eng, rank, world_size, grad_buf, shadow_buf, pads)
+    sync = NVLinkGradSync(eng, rank, world_size, grad_buf, shadow_buf, pads, red_buf)
     # first launch of the pad kernels happens here, eagerly, not inside a later CUDA-graph capture
     pads.barrier()
     torch.cuda.synchronize()

@@ -185,9 +185,8 @@ class DistributedTrainer:
         self._loss_acc.zero_()
         for m in range(ga):
             ids = input_ids[m * micro:(m + 1) * micro]
-            last = m == ga - 1
             if self.grad_sync is not None:
-                self.grad_sync.begin_micro_step(last)
+                self.grad_sync.begin_micro_step(m, ga)
             loss = eng.forward_backward(ids, ids, 1.0 / ga)
             self._loss_acc.add_(loss)
         if self.grad_sync is not None:

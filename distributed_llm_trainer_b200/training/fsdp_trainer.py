@@ -164,6 +164,8 @@ class FSDPTrainer:
                 if self.sharded is not None:
                     self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga, last=(m == ga - 1)))
                 else:
+                    if self.grad_sync is not None:
+                        self.grad_sync.begin_micro_step(m, ga)
                     self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga))
             g0 = self.optimizer.param_groups[0]
             if self.sharded is not None:

@@ -110,11 +110,16 @@ int b200_gemm2_ag_bf16(const b200_gemm_args* args, const b200_ag_args* ag, void*
  * transfer rides under the main loop of the following tiles.  After every rank has run its GEMM (and a
  * barrier), owner o holds sum_r C_r for its rows: there is no separate reduce-scatter kernel.
  *   owner_base[o]: device pointer (mapped into this process) to the first row rank o owns, row pitch args->ldc;
- *                  NULL allowed for ranks that own no slab.  args->C is ignored (may be NULL). */
+ *                  NULL allowed for ranks that own no slab.  args->C is ignored (may be NULL).
+ * Gradient accumulation: micro-steps before the last accumulate locally (b200_gemm2_bf16, reduce-add into a
+ * private buffer); the last one passes that buffer as `prev`. */
 typedef struct b200_rs_args {
   const void* const* owner_base; /* host array [world] */
   int world;                     /* 1..8 */
   int rot;                       /* rotation of the owner assignment (spreads short tensors over the ranks) */
+  const void* prev;              /* optional: this rank's own fp32 accumulator of C ([M, N], pitch args->ldc) holding
+                                    the gradient of the earlier micro-steps; when set, owner += A*B + prev, so a
+                                    step's whole local gradient crosses NVLink once, inside the last wgrad GEMM */
 } b200_rs_args;
 int b200_gemm2_rs_bf16(const b200_gemm_args* args, const b200_rs_args* rs, void* stream);
 /* The ownership rule above, for callers that lay out the owners' buffers: owner of a slab, and the slab run
@@ -290,7 +295,7 @@ int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg
                       int step, float lr, float beta1, float beta2, float eps, float weight_decay,
                       const float* grad_scale, int zero_grad, int max_ctas, void* stream);
 /* dst[pg ..] = sum_r src_r[g ..] over the chunks (small tensors that every rank accumulates locally);
- * zero_remote != 0 also clears the peers' copies for the next step. */
+ * zero_remote != 0 also clears every rank's source copy for the next step (dst may alias this rank's source). */
 int b200_pull_reduce_chunks(const void* const* src_ptrs, float* dst, const b200_chunk* chunks_dev, int n_chunks,
                             int rank, int world, int zero_remote, void* stream);
 /* b200_embed_bwd with owner-directed rows (same slab rule as b200_gemm2_rs_bf16 over `vocab` rows): owner_base[o]

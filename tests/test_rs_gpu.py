@@ -59,6 +59,31 @@ def test_gemm_rs_matches_fp32(world, shape):
         assert torch.all(layout == 3.0)
 
 
+@pytest.mark.parametrize("world", [1, 4])
+@pytest.mark.parametrize("shape,split", [((768, 768, 1024), 1), ((768, 768, 2048), 4), ((1000, 256, 384), 2),
+                                         ((2304, 768, 512), 1)])
+def test_gemm_rs_carries_local_accumulation(world, shape, split):
+    """owner += A*B + prev: the locally accumulated gradient rides in the same reduce-add (first K split only)."""
+    n_out, k_in, T = shape
+    torch.manual_seed(7)
+    dy = (torch.randn(T, n_out, device=DEV) * 0.5).to(torch.bfloat16)
+    x = (torch.randn(T, k_in, device=DEV) * 0.5).to(torch.bfloat16)
+    prev = torch.randn(n_out, k_in, device=DEV) * 30.0
+    keep = prev.clone()
+    ref = dy.float().t() @ x.float() + prev
+    g, bufs, bases = _owner_buffers(n_out, k_in, world, 2)
+    for o in range(world):          # owners already hold other ranks' contributions
+        bufs[o][1:-1].fill_(1.5)
+    rs = K.make_rs_args(bases, g.rot, prev_ptr=prev.data_ptr())
+    K.gemm(dy, x, prev, a_mn=True, b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split,
+           tile_n=256 if k_in % 256 == 0 else 128, M=n_out, N=k_in, K=T, rs=rs)
+    torch.cuda.synchronize()
+    got = _assemble(g, bufs, world)
+    err = (got - (ref + 1.5)).norm() / ref.norm()
+    assert err < 2e-3, f"rel L2 {err:.3e}"
+    assert torch.equal(prev, keep), "the local accumulator is read, never written"
+
+
 def test_slab_rule_matches_native():
     import ctypes as C
 
