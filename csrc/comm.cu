@@ -366,6 +366,28 @@ adamw_chunks_kernel(float* __restrict__ master, float* __restrict__ grad, float*
   }
 }
 
+// bf16 copy of the chunks' fp32 master values into the parameter buffer(s) of their holders, gradient cleared:
+// the device half of a step whose AdamW ran somewhere else (--cpu_offload: on the host).
+__global__ void __launch_bounds__(256)
+cast_scatter_chunks_kernel(const float* __restrict__ master, float* __restrict__ grad, PeerTable shadows, int world,
+                           int rank, const Chunk* __restrict__ ch, int nch) {
+  for (int c = blockIdx.x; c < nch; c += gridDim.x) {
+    const Chunk k = ch[c];
+    for (int i = threadIdx.x; i < (k.n >> 2); i += 256) {
+      const long long e = 4LL * i;
+      const float4 p = *reinterpret_cast<const float4*>(master + k.pg + e);
+      if (grad != nullptr) *reinterpret_cast<float4*>(grad + k.pg + e) = make_float4(0.f, 0.f, 0.f, 0.f);
+      const uint2 s = make_uint2(pack_bf16x2(p.x, p.y), pack_bf16x2(p.z, p.w));
+      if (k.dst >= 0) {
+        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(shadows.p[k.dst]) + k.sh + e) = s;
+      } else {
+        for (int r = 0; r < world; ++r)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(shadows.p[(rank + r) % world]) + k.sh + e) = s;
+      }
+    }
+  }
+}
+
 // Small tensors (norm weights) accumulate in every rank's own buffer; their owner pulls the peers' copies:
 // dst[pg ..] = sum_r src_r[g ..], and every rank's copy is cleared for the next step (zero_remote).
 __global__ void __launch_bounds__(256)
@@ -566,6 +588,18 @@ int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg
                                                          reinterpret_cast<const Chunk*>(chunks_dev), n_chunks, lr, beta1,
                                                          beta2, eps, weight_decay, (float)(lr / bc1),
                                                          (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_cast_scatter_chunks(const float* master, float* grad_to_zero, const void* const* param_ptrs, int rank, int world,
+                              const b200_chunk* chunks_dev, int n_chunks, void* stream) {
+  if (n_chunks <= 0) return 0;
+  PeerTable sh;
+  if (int rc = fill_table(&sh, param_ptrs, world)) return rc;
+  int blocks = n_chunks < sm_count() * 8 ? n_chunks : sm_count() * 8;
+  cast_scatter_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(master, grad_to_zero, sh, world, rank,
+                                                                reinterpret_cast<const Chunk*>(chunks_dev), n_chunks);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -63,6 +63,7 @@ _SIGS = {
     "b200_sumsq_chunks": [_P, _P, _I, _P, _F, _P],
     "b200_adamw_chunks": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _F, _F, _F, _F, _F, _P, _I, _I, _P],
     "b200_pull_reduce_chunks": [_P, _P, _P, _I, _I, _I, _I, _P],
+    "b200_cast_scatter_chunks": [_P, _P, _P, _I, _I, _P, _I, _P],
     "b200_embed_bwd_rs": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "b200_gemm2_ag_bf16": [C.POINTER(GemmArgs), C.POINTER(AgArgs), _P],
     "b200_gemm_bf16": [C.POINTER(GemmArgs), _P],
@@ -364,6 +365,11 @@ def adamw_chunks(master, grad, exp_avg, exp_avg_sq, param_ptrs, rank, world, dec
     _call("b200_adamw_chunks", master.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), param_ptrs,
           rank, world, decay_chunks.data_ptr(), table.data_ptr(), n_chunks, step, lr, beta1, beta2, eps, wd,
           _ptr(grad_scale), int(zero_grad), max_ctas, _stream())
+
+
+def cast_scatter_chunks(master, grad_to_zero, param_ptrs, rank, world, table, n_chunks):
+    _call("b200_cast_scatter_chunks", master.data_ptr(), _ptr(grad_to_zero), param_ptrs, rank, world, table.data_ptr(),
+          n_chunks, _stream())
 
 
 def pull_reduce_chunks(src_ptrs, dst_f32, table, n_chunks, rank, world, zero_remote: bool = True):

@@ -12,13 +12,16 @@ NO_SHARD (:269-274), bf16 parameters + communication with fp32 sharded master we
       ``b200_memcpy_async``; optionally the ``b200_all_gather_bf16`` pull kernel) into a pooled unit
       buffer on a gather stream (next unit prefetched while the current one computes; FULL_SHARD
       frees it after use and gathers again in backward, SHARD_GRAD_OP keeps it);
-    * wgrad GEMMs write fp32 gradients into peer-mapped per-block buffers that accumulate over the
-      micro-steps of a step; on the last micro-step each rank copies the peers' versions of *its*
-      slice over and sums them into the sharded fp32 gradient (``b200_reduce_scatter_f32_accum``).
-      ``B200_FSDP_ACCUM_LOCAL=0`` reduces every micro-step through two rotating staging buffers
-      instead, as FSDP1 does (the reference has no ``no_sync``);
-    * the step is: sharded norm^2 -> pad all-reduce -> clip coefficient -> fused AdamW on the shard,
-      writing the bf16 slice peers will gather next step.
+    * gradients and optimizer state follow a second partition, 128-row slabs of every weight matrix
+      (``parallel/ownership.py``): micro-steps before the last accumulate into this rank's own flat fp32
+      buffer, and the LAST micro-step's wgrad GEMMs reduce-add accumulator + product straight into the
+      owners' buffers over NVLink (``b200_gemm2_rs_bf16``) -- the reduce-scatter is the epilogue of the
+      GEMM that produces the gradient, one crossing per step (``B200_FSDP_ACCUM_LOCAL=0``: every
+      micro-step delivers, as FSDP1 does; the reference has no ``no_sync``);
+    * the step is: barrier -> norm^2 of the owned rows -> pad all-reduce -> clip coefficient -> ONE
+      fused AdamW launch that writes the new bf16 values into the parameter shards of whichever
+      ranks hold them (``b200_adamw_chunks``) -> barrier.  A micro-step contains no cross-rank
+      synchronisation, so all of them replay from CUDA graphs.
 
 ``TorchShardedModel`` (PyTorch path: CPU/gloo tests)
     same sharding arithmetic and optimizer on top of autograd + ``torch.distributed`` collectives.
@@ -148,36 +151,50 @@ class ShardedGPT:
             cur += part
         self.shard_total = cur
         self.pads = SignalPads(dev)
-        # bf16 shard (peers pull from it) and sharded fp32 gradient accumulator
+        # bf16 parameter shards (what peers gather from): flat 1/N slices of every unit
         self.shard_bf16 = SymmetricBuffer(self.shard_total, torch.bfloat16, dev)
-        self.grad_shard = torch.zeros(self.shard_total, dtype=torch.float32, device=dev)
-        self.master_shard = torch.zeros(self.shard_total, dtype=torch.float32, device=dev)
+        # Gradient / optimizer ownership is a different partition: 128-row slabs of every weight matrix
+        # (parallel/ownership.py), so that the wgrad GEMMs can reduce-add their tiles straight into the owner's
+        # buffer.  An owner keeps the fp32 master copy, both AdamW moments and the reduced gradient of its rows,
+        # stored back to back in flat order ("owner layout"); its AdamW launch writes the new bf16 values into
+        # whichever rank's parameter shard holds them.
+        from .ownership import OwnershipPlan
+
+        self.plan = OwnershipPlan(st.slots, world)
+        self.own_ranges_all = self.plan.all_ranges()
+        self.own_ranges = self.own_ranges_all[rank]
+        self.own_off: List[int] = []
+        cur = 0
+        for a_, b_ in self.own_ranges:
+            self.own_off.append(cur)
+            cur += b_ - a_
+        self.own_total = cur
+        own_max = max(sum(b_ - a_ for a_, b_ in rr) for rr in self.own_ranges_all)
+        self.red_buf = SymmetricBuffer(max(own_max, ALIGN), torch.float32, dev)    # owners' rows: cross-rank sums land here
+        self.master_shard = torch.zeros(max(self.own_total, ALIGN), dtype=torch.float32, device=dev)
         self.keep_full_master = os.environ.get("B200_FSDP_FULL_MASTER", "0") == "1"
         self._refresh_shard_from_master()
         self.release_full_master()
         # pools
         blk = max(self.unit_part[1:]) * world if self.L > 0 else ALIGN
         root = self.unit_part[0] * world
-        n_gather = self.L if strategy == "SHARD_GRAD_OP" else min(self.L, 3)
+        # limit_all_gathers (reference fsdp_trainer.py:306): True = at most one gather in flight beyond the unit
+        # being computed (3 pooled buffers); False = prefetch two units ahead (more buffers, more NVLink overlap)
+        self.limit_all_gathers = bool(limit_all_gathers)
+        self.backward_prefetch = bool(backward_prefetch)
+        depth = 3 if self.limit_all_gathers else 5
+        n_gather = self.L if strategy == "SHARD_GRAD_OP" else min(self.L, depth)
         slack = 64 * model.config.hidden_size   # the LM-head GEMM's last B tile may read past V rows
         self.root_w = torch.zeros(root + slack, dtype=torch.bfloat16, device=dev)
         self.gather_pool = [torch.zeros(blk, dtype=torch.bfloat16, device=dev) for _ in range(max(n_gather, 1))]
-        self.root_g = SymmetricBuffer(root, torch.float32, dev)
-        # Gradient accumulation across micro-steps.  accum_local (default when it fits): every block unit has its own
-        # peer-mapped fp32 buffer that accumulates over the micro-steps of a step and is reduce-scattered ONCE, on
-        # the last one -- 180 GB of HBM makes the reference's "reduce-scatter every micro-step" (FSDP1 without
-        # no_sync, fsdp_trainer.py:369-384) an avoidable cost: GA x less traffic and GA x fewer barriers.
-        # B200_FSDP_ACCUM_LOCAL=0 restores the per-micro-step reduction through two rotating staging buffers
-        # (gradient memory / world, the reference's footprint).
-        full_bytes = 4 * blk * self.L
-        free_b, _tot = torch.cuda.mem_get_info(dev)
-        self.accum_local = (os.environ.get("B200_FSDP_ACCUM_LOCAL", "1") != "0" and self.L > 0
-                            and full_bytes < 0.25 * free_b)
-        n_stage = self.L if self.accum_local else 2
-        self.grad_pool = [SymmetricBuffer(blk, torch.float32, dev) for _ in range(n_stage)]
-        self.comm_stream = torch.cuda.Stream(device=dev)     # gradient reductions (barrier / copy / sum / barrier)
-        # Parameter gathers get their own stream: queued behind a reduction they would wait for that reduction's
-        # barrier, i.e. for the slowest peer's backward, and stall the next block's weights_hook.
+        # This rank's own fp32 gradient accumulator (flat, full size): the micro-steps before the last add into it
+        # locally; the last micro-step's wgrad GEMMs send accumulator + product to the owners, so a step's gradient
+        # crosses NVLink once (the reference reduce-scatters every micro-step, fsdp_trainer.py:369-384;
+        # B200_FSDP_ACCUM_LOCAL=0 does the same here: every micro-step delivers to the owners).  Peer-mapped only so
+        # that owners can pull the few norm-weight gradients.
+        self.acc_buf = SymmetricBuffer(st.total, torch.float32, dev)
+        self.accum_local = os.environ.get("B200_FSDP_ACCUM_LOCAL", "1") != "0"
+        # Parameter gathers run on their own stream, prefetched ahead of the compute walk.
         self.gather_stream = torch.cuda.Stream(device=dev)
         self._params_ready: Optional[torch.cuda.Event] = None   # recorded after the optimizer step's barrier
         self.max_ctas = 0
@@ -188,13 +205,10 @@ class ShardedGPT:
         self.qkv_off = (st.by_name["layers.0.attention.q_proj.weight"].offset - self.units[1].lo) if self.L > 0 else 0
         # Unit all-gathers ride the copy engines by default (B200_FSDP_CE_GATHER=0: the P2P-pull SM kernel).
         self.ce_gather = os.environ.get("B200_FSDP_CE_GATHER", "1") != "0"
-        # Same for the gradient reduce-scatter: copy-engine transfer + local sum (B200_FSDP_CE_RS=0: P2P-pull kernel)
-        self.ce_rs = os.environ.get("B200_FSDP_CE_RS", "1") != "0"
-        self._rs_tmp: Dict[int, List[torch.Tensor]] = {}
         self.use_graphs = (os.environ.get("B200_FSDP_GRAPHS", "1") != "0"
                            and os.environ.get("B200_NO_GRAPHS", "0") != "1")
         self._graphs: Dict[Tuple[int, int, float], Any] = {}
-        self._plain_calls = 0
+        self._plain_calls: Dict[Any, int] = {}
         # The fused all-gather GEMM is opt-in (B200_FSDP_FUSE_AG=1): a PREFETCHED gather hides completely under
         # the previous block's compute, the fused one only under its own GEMM -- measured +7 ms / step on the
         # 355M benchmark at 2 GPUs (profiles/fsdp_comm_breakdown.md).  It pays when nothing precedes the GEMM.
@@ -211,21 +225,65 @@ class ShardedGPT:
         self._gathered: Dict[int, Tuple[int, torch.cuda.Event]] = {}   # layer -> (pool slot, ready event)
         self._slot_free_evt: List[Optional[torch.cuda.Event]] = [None] * len(self.gather_pool)
         self._slot_owner: List[Optional[int]] = [None] * len(self.gather_pool)
-        self._gslot_free_evt: List[Optional[torch.cuda.Event]] = [None] * len(self.grad_pool)
         self._root_ready: Optional[torch.cuda.Event] = None
         self._phase = "idle"
+        self._build_owner_tables()
         torch.cuda.synchronize()
         dist.barrier()
 
     # ------------------------------------------------------------------------------------------ setup helpers
     def _refresh_shard_from_master(self) -> None:
-        """Full fp32 parameters (materialised) -> this rank's fp32 master shard and bf16 shard."""
+        """Full fp32 parameters (materialised) -> this rank's fp32 master rows (owner layout) and its bf16 parameter
+        shard (flat-slice layout)."""
         st = self.store
         with torch.no_grad():
+            for (a, b), off in zip(self.own_ranges, self.own_off):
+                self.master_shard[off: off + b - a].copy_(st.master[a:b])
             for u, (a, b) in zip(range(len(self.units)), self.ranges):
                 off = self.shard_off[u]
-                self.master_shard[off: off + b - a].copy_(st.master[a:b])
                 self.shard_bf16.local[off: off + b - a].copy_(st.master[a:b])
+
+    def _build_owner_tables(self) -> None:
+        """Owner tables for the wgrad GEMMs (where every rank keeps its rows of each weight gradient) and the chunk
+        tables of the optimizer launch (owner layout -> flat-slice parameter shards)."""
+        from ..ops import kernels as K
+
+        rank, world = self.rank, self.world
+        # compact offset of every owned range, per rank
+        off_of = []
+        for rr in self.own_ranges_all:
+            d, cur = {}, 0
+            for a, b in rr:
+                d[a] = cur
+                cur += b - a
+            off_of.append(d)
+        self._rs: Dict[Tuple[str, bool], tuple] = {}
+        for key, g in self.plan.groups.items():
+            bases = []
+            for o in range(world):
+                lo, hi = g.flat_range(o, world)
+                bases.append(self.red_buf.raw_ptrs[o] + 4 * off_of[o][lo] if hi > lo else None)
+            self._rs[(key, False)] = K.make_rs_args(bases, g.rot)
+            self._rs[(key, True)] = K.make_rs_args(bases, g.rot, prev_ptr=self.acc_buf.raw_ptrs[rank] + 4 * g.offset)
+        self.engine.rs_router = lambda key, prev: self._rs.get((key, bool(prev)))
+        # AdamW runs: split every owned range where the flat-slice holder of the bf16 parameters changes
+        runs = []
+        unit_of = []
+        for u, un in enumerate(self.units):
+            unit_of.append((un.lo, un.hi, u))
+        for (a, b), off in zip(self.own_ranges, self.own_off):
+            u = next(i for lo, hi, i in unit_of if lo <= a < hi)
+            ulo, part = self.units[u].lo, self.unit_part[u]
+            f = a
+            while f < b:
+                dst = (f - ulo) // part
+                end = min(b, ulo + (dst + 1) * part)
+                runs.append((f, off + (f - a), off + (f - a), self.shard_off[u] + (f - ulo - dst * part), end - f, dst))
+                f = end
+        self._chunks = K.make_chunk_table(runs, self.device)
+        small = {lo for lo, _ in self.plan.small_ranges(rank)}
+        pulls = [(a, off, 0, 0, b - a, -1) for (a, b), off in zip(self.own_ranges, self.own_off) if a in small]
+        self._pull_chunks = K.make_chunk_table(pulls, self.device)
 
     # The fp32 master weights are sharded like everything else: outside of checkpoint save / load only
     # ``master_shard`` (1/N of the model) exists and the module's parameters point at empty storage.
@@ -246,14 +304,14 @@ class ShardedGPT:
         st = self.store
         if st.master.numel() == st.total:
             if self.keep_full_master:
-                for u, (a, b) in enumerate(self.ranges):
-                    st.master[a:b].copy_(self.master_shard[self.shard_off[u]: self.shard_off[u] + b - a])
+                for (a, b), off in zip(self.own_ranges, self.own_off):
+                    st.master[a:b].copy_(self.master_shard[off: off + b - a])
             return
         st.master = torch.zeros(st.total, dtype=torch.float32, device=self.device)
         for p, s in zip(st.params, st.slots):
             p.data = st.master[s.offset: s.offset + s.numel].view(s.shape)
-        for u, (a, b) in enumerate(self.ranges):
-            st.master[a:b].copy_(self.master_shard[self.shard_off[u]: self.shard_off[u] + b - a])
+        for (a, b), off in zip(self.own_ranges, self.own_off):
+            st.master[a:b].copy_(self.master_shard[off: off + b - a])
 
     def _views(self, buf: torch.Tensor, l: int, LayerWeights):
         """LayerWeights views into a gathered/staging unit buffer for block l (offsets relative to the unit)."""
@@ -297,7 +355,8 @@ class ShardedGPT:
         e.hooks_capturable = False
         e.rs_router = None
         e.max_ctas = 0
-        e.wgrad_overwrite = not self.accum_local    # rotating staging buffers hold one contribution per use
+        e.wgrad_overwrite = False
+        e.grad_mode = "add"
         e.sm_count = torch.cuda.get_device_properties(self.device).multi_processor_count
         self._LayerWeights = LayerWeights
         st = self.store
@@ -309,13 +368,24 @@ class ShardedGPT:
 
         e.w_emb = rootv(self.root_w, "embed_tokens.weight")
         e.w_norm = rootv(self.root_w, "norm.weight")
-        e.g_emb = rootv(self.root_g.local, "embed_tokens.weight")
-        e.g_norm = rootv(self.root_g.local, "norm.weight")
-        e.w_layers, e.g_layers = [], [None] * self.L
+        acc = self.acc_buf.local
+        e.g_emb = st.view(acc, "embed_tokens.weight")
+        e.g_norm = st.view(acc, "norm.weight")
+        e.w_layers = []
+        e.g_layers = []
+        for l in range(self.L):        # gradient views into this rank's flat accumulator (as the DDP engine's)
+            pre = f"layers.{l}."
+            e.g_layers.append(LayerWeights(
+                ln1=st.view(acc, pre + "input_layernorm.weight"),
+                wqkv=st.packed(acc, [pre + f"attention.{n}_proj.weight" for n in "qkv"]),
+                wo=st.view(acc, pre + "attention.o_proj.weight"),
+                ln2=st.view(acc, pre + "post_attention_layernorm.weight"),
+                wgu=st.packed(acc, [pre + "mlp.gate_proj.weight", pre + "mlp.up_proj.weight"]),
+                wd=st.view(acc, pre + "mlp.down_proj.weight")))
         e.ag_hook = self._ag_hook
         e.weights_hook = self._weights_hook
         e.release_hook = self._release_hook
-        e.grad_ready_hook = self._grad_ready_hook
+        e.grad_ready_hook = None
 
     # ------------------------------------------------------------------------------------------ gathers
     def _unit_ptrs(self, u: int):
@@ -397,9 +467,16 @@ class ShardedGPT:
             self._prefetch(l)
         slot, ev, _ = self._gathered[l]
         torch.cuda.current_stream().wait_event(ev)
-        # prefetch the unit the walk needs next
-        nxt = l + 1 if self._phase == "forward" else l - 1
-        self._prefetch(nxt)
+        # prefetch the unit(s) the walk needs next: forward always (FSDP's forward_prefetch), backward only with
+        # backward_prefetch=BACKWARD_PRE (reference fsdp_trainer.py:291-307); limit_all_gathers=False looks two ahead
+        if self._phase == "forward":
+            self._prefetch(l + 1)
+            if not self.limit_all_gathers:
+                self._prefetch(l + 2)
+        elif self.backward_prefetch:
+            self._prefetch(l - 1)
+            if not self.limit_all_gathers:
+                self._prefetch(l - 2)
         return self._views(self.gather_pool[slot], l, self._LayerWeights)
 
     def _free_gathered(self, l: int) -> None:
@@ -409,114 +486,53 @@ class ShardedGPT:
         self._slot_free_evt[slot] = ev
         self._slot_owner[slot] = None
 
-    # ------------------------------------------------------------------------------------------ grad staging
-    def _stage_for(self, l: int):
-        slot = l if self.accum_local else (l & 1)
-        ev = self._gslot_free_evt[slot]
-        if ev is not None:
-            torch.cuda.current_stream().wait_event(ev)
-        # no zero-fill: wgrad GEMMs overwrite (engine.wgrad_overwrite), the two norm gradients are cleared by
-        # the caller, and the alignment padding between parameters is never written after allocation
-        return slot, self.grad_pool[slot]
-
-    def _reduce_unit(self, u: int, staging) -> torch.cuda.Event:
-        """comm stream: barrier (all ranks produced unit u) -> reduce own slice -> barrier (all done reading)."""
-        from ..ops import kernels as K
-
-        cs = self.comm_stream
-        done = torch.cuda.Event()
-        produced = torch.cuda.Event()
-        produced.record(torch.cuda.current_stream())
-        cs.wait_event(produced)
-        with torch.cuda.stream(cs):
-            self.pads.barrier()
-            part = self.unit_part[u]
-            lo = self.rank * part
-            n = min(part, max(0, (self.units[u].hi - self.units[u].lo) - lo))
-            n = (n + 3) // 4 * 4
-            dst = self.grad_shard[self.shard_off[u]: self.shard_off[u] + part]
-            if n > 0 and self.ce_rs and self.world > 1:
-                # Copy engines bring the peers' copies of this rank's slice next to the local one; the sum is
-                # then a local streaming kernel.  The SMs never stall on NVLink loads and the transfer does not
-                # occupy the SMs the persistent GEMM / attention CTAs are using.
-                tmps = self._rs_tmp.get(part)      # shared by all units of this size: reductions are stream-ordered
-                if tmps is None:
-                    tmps = [torch.empty(part, dtype=torch.float32, device=self.device) for _ in range(self.world - 1)]
-                    self._rs_tmp[part] = tmps
-                tab, k = [], 0
-                for r in range(self.world):
-                    if r == self.rank:
-                        tab.append(staging.raw_ptrs[r])
-                    else:
-                        K.memcpy_async(tmps[k].data_ptr(), staging.raw_ptrs[r] + 4 * lo, 4 * n)
-                        tab.append(tmps[k].data_ptr() - 4 * lo)     # the kernel indexes every source at `lo`
-                        k += 1
-                K.reduce_scatter_f32_accum(K.ptr_array(tab), dst, lo, n, 1.0 / self.world, self.rank, self.world,
-                                           self.max_ctas)
-            elif n > 0:
-                K.reduce_scatter_f32_accum(staging.ptrs, dst, lo, n, 1.0 / self.world, self.rank, self.world,
-                                           self.max_ctas)
-            self.pads.barrier()
-            if self.accum_local:
-                staging.local.zero_()      # every peer has read its slice: start the next step's accumulation at 0
-            done.record(cs)
-        return done
-
     def _release_hook(self, l: int, phase: str) -> None:
         if phase == "forward":
             if self.strategy == "FULL_SHARD":
                 self._free_gathered(l)
             return
-        # backward of block l finished: its staging buffer holds this rank's full-unit gradient
-        if self.accum_local:
-            if self._last_micro:
-                self._gslot_free_evt[l] = self._reduce_unit(1 + l, self.grad_pool[l])
-        else:
-            slot = l & 1
-            self._gslot_free_evt[slot] = self._reduce_unit(1 + l, self.grad_pool[slot])
-        self._free_gathered(l)
-
-    def _grad_ready_hook(self, unit: int) -> None:
-        if unit == 0 and (self._last_micro or not self.accum_local):
-            self._root_done = self._reduce_unit(0, self.root_g)
+        self._free_gathered(l)         # backward of block l finished: its gathered weights are dead
 
     # ------------------------------------------------------------------------------------------ micro-step
     def forward_backward(self, input_ids: torch.Tensor, labels: torch.Tensor, loss_scale: float,
-                         last: bool = True) -> torch.Tensor:
-        """One micro-step.  ``last``: this is the final micro-step before ``step()`` -- with local accumulation the
-        gradient reduce-scatter only happens then (callers that never pass it reduce every micro-step).
+                         last: bool = True, first: Optional[bool] = None) -> torch.Tensor:
+        """One micro-step.  ``first`` / ``last``: position inside the optimizer step -- the first micro-step overwrites
+        this rank's gradient accumulator, the middle ones add to it, and the last one's wgrad GEMMs send accumulator +
+        product to the rows' owners (callers that pass neither deliver every micro-step).
 
-        Micro-steps without a reduction are pure compute + copy-engine gathers with a fixed host-side schedule
-        (pool slots, events), so from the third one on they are replayed from a CUDA graph that spans the main
-        and the gather stream (B200_FSDP_GRAPHS=0 / B200_NO_GRAPHS=1: always eager)."""
+        A micro-step is pure compute + copy-engine gathers with a fixed host-side schedule (pool slots, events) and
+        contains no cross-rank synchronisation -- the reduce-adds into the owners are ordinary TMA stores of the wgrad
+        kernels -- so from the third call on every kind of micro-step is replayed from a CUDA graph that spans the
+        main and the gather stream (B200_FSDP_GRAPHS=0 / B200_NO_GRAPHS=1: always eager)."""
         from ..ops import kernels as K
 
-        self._last_micro = bool(last)
         e = self.engine
+        if first is None:
+            first = bool(last)
+        if not self.accum_local or (first and last):
+            e.grad_mode = "rs1"
+        else:
+            e.grad_mode = "store" if first else ("rs" if last else "add")
         B, S = input_ids.shape
         ws = e.workspace(B, S, True)
         e._load_inputs(ws, input_ids, labels)
         cur = torch.cuda.current_stream()
-        # root unit: gathered once per micro-step, stays resident (as FSDP's root does)
-        if getattr(self, "_root_done", None) is not None:
-            cur.wait_event(self._root_done)
-            self._root_done = None
+        # root unit: gathered once per optimizer step, stays resident (as FSDP's root does)
         if getattr(self, "_root_stale", True):
+            if self._params_ready is not None:
+                cur.wait_event(self._params_ready)
             self._gather_unit(0, self.root_w)       # parameters only change at the optimizer step
             self._root_stale = False
-        if not self.accum_local:
-            self.root_g.local.zero_()               # accum_local: zeroed on the comm stream after each reduction
-        if not (self.use_graphs and self.accum_local and not last and not self.fuse_ag):
+        if not (self.use_graphs and not self.fuse_ag):
             self._micro_body(ws, loss_scale)
             return ws.loss_sum
-        key = (B, S, float(loss_scale))
+        key = (B, S, float(loss_scale), e.grad_mode)
         entry = self._graphs.get(key)
-        self._plain_calls += 1
-        if entry is None and self._plain_calls > 2:
-            # every dependency inside the capture must be on captured work: join the side streams and drop the
+        self._plain_calls[key] = self._plain_calls.get(key, 0) + 1
+        if entry is None and self._plain_calls[key] > 2:
+            # every dependency inside the capture must be on captured work: join the side stream and drop the
             # events of earlier (eager) micro-steps -- stream order of the graph launch covers them
             cur.wait_stream(self.gather_stream)
-            cur.wait_stream(self.comm_stream)
             torch.cuda.synchronize()
             self._drop_events()
             g = torch.cuda.CUDAGraph()
@@ -531,13 +547,15 @@ class ShardedGPT:
         if entry is None:
             self._micro_body(ws, loss_scale)
         else:
+            if self._params_ready is not None:      # first replay after an optimizer step: peers' new shards are ready
+                cur.wait_event(self._params_ready)
+                self._params_ready = None
             entry[0].replay()
             K.launch_count += entry[1]
         return ws.loss_sum
 
     def _drop_events(self) -> None:
         self._slot_free_evt = [None] * len(self.gather_pool)
-        self._gslot_free_evt = [None] * len(self.grad_pool)
         self._params_ready = None
 
     def _micro_body(self, ws, loss_scale: float) -> None:
@@ -552,93 +570,98 @@ class ShardedGPT:
         self._prefetch(0)
         e._forward_body(ws, True)
         self._phase = "backward"
-        self._prefetch(self.L - 1)                  # BACKWARD_PRE: overlaps the LM head
+        if self.backward_prefetch:
+            self._prefetch(self.L - 1)              # BACKWARD_PRE: overlaps the LM head
         e._lm_head_loss(ws, loss_scale, with_grad=True)
-        # engine backward with per-block staging buffers
-        L = self.L
         e._final_norm_bwd(ws)
-        for l in reversed(range(L)):
-            slot, staging = self._stage_for(l)
-            g = self._views(staging.local, l, self._LayerWeights)
-            if not self.accum_local:
-                g.ln1.zero_()       # RMSNorm weight gradients accumulate with atomics
-                g.ln2.zero_()
-            e.g_layers[l] = g
+        for l in reversed(range(self.L)):
             if e.checkpointing:
                 e._layer_fwd(l, ws, ws.x[l], None, True, skip_last=True)
             e._layer_bwd(l, ws, ws.x[l])
             self._release_hook(l, "backward")
-        K.embed_bwd(ws.ids, ws.dx, e.g_emb)
-        self._grad_ready_hook(0)
+        e._embed_bwd(ws)
         K.rng_advance(e.rng_state, 1)
         self._phase = "idle"
 
     # ------------------------------------------------------------------------------------------ optimizer step
     def step(self, opt_state, lr: float, betas, eps: float, wd: float, grad_clip: float,
              norm_out: Optional[torch.Tensor] = None) -> None:
-        """Sharded clip + AdamW.  ``opt_state`` = dict(exp_avg, exp_avg_sq, step, grad_scale, decay)."""
+        """Sharded clip + AdamW over the rows this rank owns.  ``opt_state`` = dict(exp_avg, exp_avg_sq, step,
+        grad_scale, decay), moments in owner layout.  The reduce-scatter has already happened inside the last
+        micro-step's wgrad GEMMs; what is left is: barrier (all reduce-adds landed) -> owners pull the norm-weight
+        gradients -> squared norm -> scalar all-reduce -> clip coefficient -> ONE AdamW launch that writes the new
+        bf16 values into the parameter shards of whichever ranks hold them and clears the gradient -> barrier."""
         from ..ops import kernels as K
 
         cur = torch.cuda.current_stream()
-        cur.wait_stream(self.comm_stream)
         cur.wait_stream(self.gather_stream)         # no gather may still be reading the shards AdamW rewrites
         self.sumsq.zero_()
-        K.sumsq(self.grad_shard, 0, self.shard_total, self.sumsq[0:1])
+        self.pads.barrier()
+        red = self.red_buf.local
+        table, n = self._pull_chunks
+        K.pull_reduce_chunks(self.acc_buf.ptrs, red, table, n, self.rank, self.world, zero_remote=True)
+        table, n = self._chunks
+        K.sumsq_chunks(red, table, n, self.sumsq[0:1], 1.0)
         self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)
-        K.clip_coef(self.sumsq_total, float(grad_clip), 1.0, opt_state["grad_scale"], norm_out)
+        # the buffers hold SUMS over ranks: the 1/world of the mean is folded into the clip coefficient
+        K.clip_coef(self.sumsq_total, float(grad_clip), 1.0 / self.world, opt_state["grad_scale"], norm_out)
         opt_state["step"] += 1
-        st = self.store
         b1, b2 = betas
         if self.cpu_offload:
             self._step_offloaded(opt_state, lr, b1, b2, eps, wd)
-            self.grad_shard.zero_()
-            self.pads.barrier()
-            self._params_ready = torch.cuda.Event()
-            self._params_ready.record(cur)
-            self._root_done = None
-            self._root_stale = True
-            return
-        for u, (a, b) in enumerate(self.ranges):
-            if b <= a:
-                continue
-            off = self.shard_off[u]
-            # every buffer is addressed so that flat element index a lands on this unit's slice of the shard
-            K.adamw_step_ptr(self.master_shard.data_ptr() + (off - a) * 4, self.grad_shard.data_ptr() + (off - a) * 4,
-                             opt_state["exp_avg"].data_ptr() + off * 4, opt_state["exp_avg_sq"].data_ptr() + off * 4,
-                             self.shard_bf16.local.data_ptr() + (off - a) * 2, opt_state["decay"].data_ptr(), a,
-                             a + (b - a + 3) // 4 * 4, opt_state["step"], lr, b1, b2, eps, wd,
-                             opt_state["grad_scale"].data_ptr())
-        self.grad_shard.zero_()
-        # peers may gather my new slices only after every rank finished its update
+        else:
+            K.adamw_chunks(self.master_shard, red, opt_state["exp_avg"], opt_state["exp_avg_sq"], self.shard_bf16.ptrs,
+                           self.rank, self.world, opt_state["decay"], table, n, opt_state["step"], lr, b1, b2, eps, wd,
+                           opt_state["grad_scale"], zero_grad=True, max_ctas=self.max_ctas)
+        # peers may gather the new shards (and send the next step's gradients) only after every rank finished
         self.pads.barrier()
         self._params_ready = torch.cuda.Event()
         self._params_ready.record(cur)
-        self._root_done = None
         self._root_stale = True
 
     # ------------------------------------------------------------------------------------------ CPU offload
     def _step_offloaded(self, opt_state, lr, b1, b2, eps, wd) -> None:
         """``--cpu_offload`` (reference: ``CPUOffload(offload_params=True)``, fsdp_trainer.py:300-301): the fp32
-        master shard and both AdamW moments live in pinned host memory; the clipped gradient shard goes
-        device -> host, AdamW runs on the CPU, the new bf16 shard comes back host -> device."""
+        master rows and both AdamW moments live in pinned host memory.  The owned gradient goes device -> host in
+        pieces on a side stream while the host runs AdamW on the previous piece and the updated master rows of the
+        piece before that travel back (pinned double buffering, three stages in flight); one device launch then
+        casts the new values into the holders' bf16 parameter shards and clears the gradient."""
+        from ..ops import kernels as K
         from ..ops.optim import adamw_reference_
 
+        n = self.own_total
         if not hasattr(self, "_host"):
             pin = dict(dtype=torch.float32, pin_memory=True)
-            master = torch.empty(self.shard_total, **pin)
-            master.copy_(self.master_shard)
-            self._host = {"master": master, "grad": torch.empty(self.shard_total, **pin),
-                          "bf16": torch.empty(self.shard_total, dtype=torch.bfloat16, pin_memory=True)}
+            master = torch.empty(n, **pin)
+            master.copy_(self.master_shard[:n])
+            self._host = {"master": master, "grad": torch.empty(n, **pin), "stream": torch.cuda.Stream(device=self.device)}
         host = self._host
-        scaled = self.grad_shard * opt_state["grad_scale"]          # clip coefficient applied on the device
-        host["grad"].copy_(scaled, non_blocking=True)
-        torch.cuda.current_stream().synchronize()
+        side = host["stream"]
+        red = self.red_buf.local
+        red[:n].mul_(opt_state["grad_scale"])                     # clip coefficient (and 1/world) applied on the device
+        side.wait_stream(torch.cuda.current_stream())
+        pieces = max(1, min(8, n // (1 << 20)))
+        bounds = [n * i // pieces // 4 * 4 for i in range(pieces)] + [n]
+        d2h = []
+        with torch.cuda.stream(side):
+            for i in range(pieces):
+                a, b = bounds[i], bounds[i + 1]
+                host["grad"][a:b].copy_(red[a:b], non_blocking=True)
+                ev = torch.cuda.Event()
+                ev.record(side)
+                d2h.append(ev)
         m, v = opt_state["exp_avg"], opt_state["exp_avg_sq"]       # host tensors in this mode
         ones = torch.ones(1)
-        adamw_reference_(host["master"], host["grad"], m, v, ones, opt_state["step"], lr, b1, b2, eps, wd, 1.0)
-        host["bf16"].copy_(host["master"])
-        self.shard_bf16.local.copy_(host["bf16"], non_blocking=True)
-        self.master_shard.copy_(host["master"], non_blocking=True)   # device copy of the shard (checkpoints read it)
+        for i in range(pieces):
+            a, b = bounds[i], bounds[i + 1]
+            d2h[i].synchronize()                                    # piece i is on the host; pieces > i still in flight
+            adamw_reference_(host["master"][a:b], host["grad"][a:b], m[a:b], v[a:b], ones, opt_state["step"], lr, b1, b2,
+                             eps, wd, 1.0)
+            with torch.cuda.stream(side):                           # H2D of piece i overlaps the host AdamW of piece i+1
+                self.master_shard[a:b].copy_(host["master"][a:b], non_blocking=True)
+        torch.cuda.current_stream().wait_stream(side)
+        table, nch = self._chunks
+        K.cast_scatter_chunks(self.master_shard, red, self.shard_bf16.ptrs, self.rank, self.world, table, nch)
 
     # ------------------------------------------------------------------------------------------ checkpoints
     def gather_full_master(self) -> None:
@@ -646,17 +669,17 @@ class ShardedGPT:
         Call ``release_full_master()`` when done with them."""
         st = self.store
         self.materialize_full_master()
-        pieces = [self.master_shard[self.shard_off[u]: self.shard_off[u] + b - a] for u, (a, b) in enumerate(self.ranges)]
-        _gather_ranges(self.all_ranges, self.world, pieces, st.master)
+        pieces = [self.master_shard[off: off + b - a] for (a, b), off in zip(self.own_ranges, self.own_off)]
+        _gather_ranges(self.own_ranges_all, self.world, pieces, st.master)
 
     def gather_flat(self, shard: torch.Tensor) -> torch.Tensor:
-        """shard-layout tensor (concatenated per-unit parts) -> full flat tensor."""
+        """owner-layout tensor (this rank's owned rows back to back) -> full flat tensor."""
         st = self.store
         full = torch.zeros(st.total, dtype=shard.dtype, device=shard.device)
-        pieces = [shard[self.shard_off[u]: self.shard_off[u] + b - a] for u, (a, b) in enumerate(self.ranges)]
-        _gather_ranges(self.all_ranges, self.world, pieces, full)
+        pieces = [shard[off: off + b - a] for (a, b), off in zip(self.own_ranges, self.own_off)]
+        _gather_ranges(self.own_ranges_all, self.world, pieces, full)
         return full
 
     def scatter_flat(self, full: torch.Tensor, shard: torch.Tensor) -> None:
-        for u, (a, b) in enumerate(self.ranges):
-            shard[self.shard_off[u]: self.shard_off[u] + b - a].copy_(full[a:b])
+        for (a, b), off in zip(self.own_ranges, self.own_off):
+            shard[off: off + b - a].copy_(full[a:b])

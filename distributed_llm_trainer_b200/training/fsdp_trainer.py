@@ -126,10 +126,10 @@ class FSDPTrainer:
             dev = self.device
             self.opt_state = {
                 # --cpu_offload keeps the moments (and the fp32 master shard) in pinned host memory
-                "exp_avg": (torch.zeros(sh.shard_total, dtype=torch.float32, pin_memory=True) if sh.cpu_offload
-                            else torch.zeros(sh.shard_total, dtype=torch.float32, device=dev)),
-                "exp_avg_sq": (torch.zeros(sh.shard_total, dtype=torch.float32, pin_memory=True) if sh.cpu_offload
-                               else torch.zeros(sh.shard_total, dtype=torch.float32, device=dev)),
+                "exp_avg": (torch.zeros(max(sh.own_total, 4), dtype=torch.float32, pin_memory=True) if sh.cpu_offload
+                            else torch.zeros(max(sh.own_total, 4), dtype=torch.float32, device=dev)),
+                "exp_avg_sq": (torch.zeros(max(sh.own_total, 4), dtype=torch.float32, pin_memory=True) if sh.cpu_offload
+                               else torch.zeros(max(sh.own_total, 4), dtype=torch.float32, device=dev)),
                 "step": 0, "grad_scale": self.optimizer.grad_scale, "decay": self.optimizer._decay,
             }
         elif self.engine is not None:
@@ -162,7 +162,7 @@ class FSDPTrainer:
             for m in range(ga):
                 ids = input_ids[m * micro:(m + 1) * micro]
                 if self.sharded is not None:
-                    self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga, last=(m == ga - 1)))
+                    self._loss_acc.add_(runner.forward_backward(ids, ids, 1.0 / ga, last=(m == ga - 1), first=(m == 0)))
                 else:
                     if self.grad_sync is not None:
                         self.grad_sync.begin_micro_step(m, ga)

@@ -294,6 +294,11 @@ int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg
                       int rank, int world, const uint8_t* decay_chunks, const b200_chunk* chunks_dev, int n_chunks,
                       int step, float lr, float beta1, float beta2, float eps, float weight_decay,
                       const float* grad_scale, int zero_grad, int max_ctas, void* stream);
+/* The parameter half of b200_adamw_chunks alone: bf16(master[pg ..]) stored to the chunks' holders, and
+ * grad_to_zero[pg ..] (may be NULL) cleared -- used when AdamW itself ran on the host (reference: FSDP
+ * CPUOffload(offload_params=True), fsdp_trainer.py:300-301). */
+int b200_cast_scatter_chunks(const float* master, float* grad_to_zero, const void* const* param_ptrs, int rank, int world,
+                             const b200_chunk* chunks_dev, int n_chunks, void* stream);
 /* dst[pg ..] = sum_r src_r[g ..] over the chunks (small tensors that every rank accumulates locally);
  * zero_remote != 0 also clears every rank's source copy for the next step (dst may alias this rank's source). */
 int b200_pull_reduce_chunks(const void* const* src_ptrs, float* dst, const b200_chunk* chunks_dev, int n_chunks,

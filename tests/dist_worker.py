@@ -378,11 +378,12 @@ def main():
         opt = parts[2] if len(parts) > 2 else ""
         if opt == "fuseag":       # QKV rows gathered inside the QKV GEMM (b200_gemm2_ag_bf16), rest prefetched
             os.environ["B200_FSDP_FUSE_AG"] = "1"
-        if opt == "smgather":     # P2P-pull SM kernels instead of copy-engine gathers / reduce-scatter transfers
+        if opt == "smgather":     # P2P-pull SM kernel instead of copy-engine gathers
             os.environ["B200_FSDP_CE_GATHER"] = "0"
-            os.environ["B200_FSDP_CE_RS"] = "0"
-        if opt == "everymicro":   # reduce-scatter every micro-step through the two rotating staging buffers
+        if opt == "everymicro":   # every micro-step's wgrad GEMMs deliver to the owners (no local accumulation)
             os.environ["B200_FSDP_ACCUM_LOCAL"] = "0"
+        if opt == "nographs":
+            os.environ["B200_FSDP_GRAPHS"] = "0"
         mode_fsdp(tmp, parts[1], offload=opt == "offload")
     elif mode == "comm":
         mode_comm(tmp)
