@@ -19,8 +19,7 @@ lse = torch.zeros(B, H, S, device="cuda")
 dqkv = torch.zeros(B * S, 3 * h, device="cuda", dtype=torch.bfloat16)
 delta = torch.zeros(B, H, S, device="cuda")
 dq_acc = torch.empty(B * S, h, device="cuda")
-fwd = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=1)
-fwd2 = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=2)
+fwd = lambda: k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9)
 bwd = lambda: k.attn_bwd(qkv, out, dout, lse, dqkv, delta, dq_acc, B, S, H, p, rng, 9)
 ang = torch.rand(S, 32, device="cuda") * 6.28
 cos, sin = ang.cos().contiguous(), ang.sin().contiguous()
@@ -30,7 +29,7 @@ bwd_then_rope = lambda: (bwd(), k.rope_inplace(dqkv, cos, sin, 2 * h, S, inverse
 fwd(); bwd(); torch.cuda.synchronize()
 if os.environ.get("ATTN_TIME", "1") == "1":
     fl = 4.0 * B * H * S * S * 64 / 2
-    tf, tb, tf2 = timeit(fwd), timeit(bwd), timeit(fwd2)
-    print(f"p={p}: fwd {tf*1e3:.1f} us ({fl/tf/1e9:.0f} TFLOP/s causal)  fwd2 {tf2*1e3:.1f} us ({fl/tf2/1e9:.0f})  bwd {tb*1e3:.1f} us ({2.5*fl/tb/1e9:.0f} TFLOP/s)")
+    tf, tb = timeit(fwd), timeit(bwd)
+    print(f"p={p}: fwd {tf*1e3:.1f} us ({fl/tf/1e9:.0f} TFLOP/s causal)  bwd {tb*1e3:.1f} us ({2.5*fl/tb/1e9:.0f} TFLOP/s)")
     tr, tu = timeit(bwd_rope), timeit(bwd_then_rope)
     print(f"p={p}: bwd + inverse RoPE fused {tr*1e3:.1f} us   unfused (bwd, then rope_inplace) {tu*1e3:.1f} us")

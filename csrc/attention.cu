@@ -48,7 +48,7 @@ constexpr float kScale2 = 0.125f * 1.4426950408889634f;
 
 struct AttnParams {
   int B, S, H;
-  int S8;                // ceil(S/8): dropout groups per score row
+  int S16;               // ceil(S/16): dropout groups (one Philox call, 8-bit lanes) per score row
   float p_drop;
   const unsigned long long* rng;
   unsigned int rng_stream;
@@ -268,8 +268,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     const int r = qd * 32 + lane;                 // row within the q tile
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
-    const uint32_t thresh_hi = dropout_threshold16(p.p_drop) << 16;
-    const float inv_keep = drop ? 1.f / (1.f - p.p_drop) : 1.f;
+    const uint32_t t4 = dropout_threshold8(p.p_drop) * 0x01010101u;
+    const float inv_keep = drop ? 1.f / dropout_keep_prob8(p.p_drop) : 1.f;
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
     float* xchg = reinterpret_cast<float*>(smem + FwdSmem::kXchg);     // [2][4][128]
@@ -284,7 +284,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       const int nkv = qi + 1;
       const int row_base = b * p.S;
       const int qrow = qi * kBlk + r;               // position in the sequence
-      const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S8;
+      const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S16;
 
       float m = -INFINITY, l = 0.f, alpha_prev = 1.f;
       float o[16];
@@ -348,21 +348,34 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         float2 l2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
         const float2 sc2 = make_float2(kScale2, kScale2), nm2 = make_float2(neg_msc, neg_msc);
 #pragma unroll
-        for (int gq = 0; gq < 4; ++gq) {
-          float pv[8];
+        for (int g16 = 0; g16 < 2; ++g16) {
+          // one Philox call = sixteen 8-bit lanes = this thread's next 16 kv positions
+          uint4 rb = make_uint4(0u, 0u, 0u, 0u);
+          if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g16 * 16) >> 4));
+          const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
 #pragma unroll
-          for (int e = 0; e < 8; e += 2) {
-            // per PAIR of elements: one FFMA2 (exponent), two MUFU, one FADD2 (row sum); masked entries are ex2(-inf) = 0
-            const float2 arg = ffma2(make_float2(__uint_as_float(v[gq * 8 + e]), __uint_as_float(v[gq * 8 + e + 1])), sc2, nm2);
-            pv[e] = ex2_ftz(arg.x);
-            pv[e + 1] = ex2_ftz(arg.y);
-            l2[(e >> 1) & 1] = fadd2(l2[(e >> 1) & 1], make_float2(pv[e], pv[e + 1]));
+          for (int hf = 0; hf < 2; ++hf) {
+            const int gq = g16 * 2 + hf;
+            float pv[8];
+#pragma unroll
+            for (int e = 0; e < 8; e += 2) {
+              // per PAIR of elements: one FFMA2 (exponent), two MUFU, one FADD2 (row sum); masked entries are ex2(-inf) = 0
+              const float2 arg = ffma2(make_float2(__uint_as_float(v[gq * 8 + e]), __uint_as_float(v[gq * 8 + e + 1])), sc2, nm2);
+              pv[e] = ex2_ftz(arg.x);
+              pv[e + 1] = ex2_ftz(arg.y);
+              l2[(e >> 1) & 1] = fadd2(l2[(e >> 1) & 1], make_float2(pv[e], pv[e + 1]));
+            }
+            uint32_t pk[4] = {pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]), pack_bf16x2(pv[4], pv[5]),
+                              pack_bf16x2(pv[6], pv[7])};
+            if (drop) {   // dropped probabilities are cleared on the packed bf16 pairs: compare 4 bytes at once, AND
+              uint32_t lo, hi;
+              keep_masks_bf16x2(w[hf * 2], t4, lo, hi);
+              pk[0] &= lo; pk[1] &= hi;
+              keep_masks_bf16x2(w[hf * 2 + 1], t4, lo, hi);
+              pk[2] &= lo; pk[3] &= hi;
+            }
+            st_shared_v4(swz(sub, r, (qt & 1) * 4 + gq), pk[0], pk[1], pk[2], pk[3]);
           }
-          if (drop)
-            dropout_zero8(dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + gq * 8) >> 3)),
-                          thresh_hi, pv);
-          st_shared_v4(swz(sub, r, (qt & 1) * 4 + gq), pack_bf16x2(pv[0], pv[1]), pack_bf16x2(pv[2], pv[3]),
-                       pack_bf16x2(pv[4], pv[5]), pack_bf16x2(pv[6], pv[7]));
         }
         l = l * alpha + ((l2[0].x + l2[0].y) + (l2[1].x + l2[1].y));
         tc_fence_before();
@@ -683,9 +696,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const int r = qd * 32 + lane;
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
-    const uint32_t thresh_hi = dropout_threshold16(p.p_drop) << 16;
-    const float log2_inv_keep = drop ? -log2f(1.f - p.p_drop) : 0.f;
-    const float keep_scale = (drop ? 1.f - p.p_drop : 1.f) * kScale;
+    const uint32_t thresh8 = dropout_threshold8(p.p_drop);   // 0 without dropout: every lane kept
+    const float keep_prob = drop ? dropout_keep_prob8(p.p_drop) : 1.f;
+    const float log2_inv_keep = -log2f(keep_prob);
+    const float keep_scale = keep_prob * kScale;
     unsigned long long seed = 0, offs = 0;
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
     const uint32_t p_sub0 = smem_u32(smem + BwdSmem::kP) + (qt >> 1) * kTile;
@@ -740,7 +754,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const float neg_lse = row_ok ? log2_inv_keep - lse_nx : -INFINITY;
         const float dl = row_ok ? dl_nx : 0.f;
         if (it + 1 < niter && qrow + kBlk < p.S) { lse_nx = lse_bh[qrow + kBlk]; dl_nx = delta_bh[qrow + kBlk]; }
-        const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S8;
+        const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S16;
         mbar_wait(sdp_full, I & 1);
         tc_fence_after();
         const uint32_t p_sub = p_sub0 + (I & 1) * kPTile, ds_sub = ds_sub0 + (I & 1) * kPTile;
@@ -768,12 +782,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
             for (int e = 0; e < 16; ++e)
               if ((qt * 32 + hh * 16 + e) > r) sv[e] = 0xFF800000u;   // -inf -> probability 0 -> dS 0
           }
+          // one Philox call (sixteen 8-bit lanes) covers this half's 16 kv positions
+          uint4 rb = make_uint4(0u, 0u, 0u, 0u);
+          if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + hh * 16) >> 4));
+          const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
 #pragma unroll
           for (int g2 = 0; g2 < 2; ++g2) {
             const int g = hh * 2 + g2;
-            uint4 rb = make_uint4(0u, 0u, 0u, 0u);   // thresh_hi is 0 without dropout: every lane kept
-            if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g * 8) >> 3));
-            const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
             float pd[8], ds[8];
 #pragma unroll
             for (int e = 0; e < 8; e += 2) {   // pairs: FFMA2 (exponent), FFMA2 (dP scale - c), FMUL2 (dS)
@@ -782,7 +797,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
               const float2 t = ffma2(make_float2(__uint_as_float(dv[g2 * 8 + e]), __uint_as_float(dv[g2 * 8 + e + 1])),
                                      make_float2(kScale, kScale), make_float2(neg_c, neg_c));
               const float qp0 = ex2_ftz(arg.x), qp1 = ex2_ftz(arg.y);
-              const bool k0 = (w[e >> 1] << 16) >= thresh_hi, k1 = w[e >> 1] >= thresh_hi;   // low / high 16-bit lane
+              const uint32_t wb = w[g2 * 2 + (e >> 2)];                                        // bytes e%4, e%4+1
+              const bool k0 = ((wb >> ((e & 3) * 8)) & 0xFFu) >= thresh8, k1 = ((wb >> ((e & 3) * 8 + 8)) & 0xFFu) >= thresh8;
               const float2 d2 = fmul2(make_float2(qp0, qp1), make_float2(k0 ? t.x : neg_c, k1 ? t.y : neg_c));
               ds[e] = d2.x;
               ds[e + 1] = d2.y;
@@ -864,7 +880,7 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
   int rc = make_tmap_2d_bf16(&tm, qkv, 3 * (uint64_t)h, (uint64_t)batch * seq, 3 * (uint64_t)h, 64, kBlk);
   if (rc) return rc;
   AttnParams p{};
-  p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
+  p.B = batch; p.S = seq; p.H = heads; p.S16 = (seq + 15) / 16; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.out = (__nv_bfloat16*)out; p.lse = lse;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   if (!configured[current_device()]) {
@@ -923,7 +939,7 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
     B200_CHECK_CUDA(cudaMemsetAsync(dq_accum, 0, size_t(rows) * h * sizeof(float), s));
   }
   AttnParams p{};
-  p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
+  p.B = batch; p.S = seq; p.H = heads; p.S16 = (seq + 15) / 16; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   if (!configured[current_device()]) {
@@ -1041,7 +1057,7 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   B200_CHECK_CUDA(cudaGetLastError());
   B200_CHECK_CUDA(cudaMemsetAsync(dq_accum, 0, size_t(rows) * h * sizeof(float), s));  // stale from the last call
   AttnParams p{};
-  p.B = batch; p.S = seq; p.H = heads; p.S8 = (seq + 7) / 8; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
+  p.B = batch; p.S = seq; p.H = heads; p.S16 = (seq + 15) / 16; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
   dim3 grid(tiles < sm_count() ? tiles : sm_count());

@@ -64,4 +64,33 @@ __device__ __forceinline__ void dropout_zero8(const uint4 r, uint32_t thresh_hi,
   }
 }
 
+// ---- 8-bit lanes: sixteen elements per Philox call (attention probabilities) ---------------------------------
+// The attention kernels draw one byte per score: a call covers 16 consecutive kv positions of a query row, which
+// halves the generator's share of the softmax instruction stream (the 16-bit form above costs ~9 thread
+// instructions per element there, RNG + compare + select).  An element is dropped when its byte < round(p * 256);
+// p = 0.1 is realised as 26/256 = 0.1016 and the kernels rescale by the REALISED keep probability
+// (dropout_keep_prob8), so the expectation of the output is exact.
+__host__ __device__ __forceinline__ uint32_t dropout_threshold8(float p) {
+  float t = p * 256.0f + 0.5f;
+  return t <= 0.f ? 0u : (t >= 255.f ? 255u : (uint32_t)t);
+}
+__host__ __device__ __forceinline__ float dropout_keep_prob8(float p) {
+  return 1.0f - float(dropout_threshold8(p)) * (1.0f / 256.0f);
+}
+// SWAR unsigned compare of the four bytes of w against a threshold replicated into every byte of t4:
+// bit 7 of byte b of the result = (w.b >= t.b).  (w | H) - (t & ~H) compares the low 7 bits without borrowing
+// across bytes; the top bits are merged with one three-input logic op.
+__device__ __forceinline__ uint32_t bytes_ge_bit7(uint32_t w, uint32_t t4) {
+  const uint32_t z = (w | 0x80808080u) - (t4 & 0x7F7F7F7Fu);
+  return (w & ~t4) | (~(w ^ t4) & z);
+}
+// keep-masks for bf16x2 words: lo = elements (4i, 4i+1), hi = elements (4i+2, 4i+3) of word w
+// (0xFFFF per kept element); prmt with the sign-replicate selector expands bit 7 of a byte.
+__device__ __forceinline__ void keep_masks_bf16x2(uint32_t w, uint32_t t4, uint32_t& lo, uint32_t& hi) {
+  const uint32_t c = bytes_ge_bit7(w, t4);
+  // (inline PTX: __byte_perm() documents only the low 3 bits of a selector nibble, the replicate bit is the 4th)
+  asm("prmt.b32 %0, %1, 0, 0x9988;" : "=r"(lo) : "r"(c));
+  asm("prmt.b32 %0, %1, 0, 0xBBAA;" : "=r"(hi) : "r"(c));
+}
+
 }  // namespace b200

@@ -247,6 +247,22 @@ __global__ void dropout_mask_kernel(uint8_t* __restrict__ mask, long long groups
   for (int e = 0; e < 8; ++e) mask[8 * g + e] = (keep >> e) & 1;
 }
 
+// attention flavour: groups of 16 along the row (ceil(cols/16) groups per row), 8-bit lanes
+__global__ void attn_dropout_mask_kernel(uint8_t* __restrict__ mask, long long rows, int cols, float p,
+                                         const unsigned long long* __restrict__ rng, uint32_t stream) {
+  const int g16 = (cols + 15) / 16;
+  const long long t = blockIdx.x * (long long)blockDim.x + threadIdx.x;
+  if (t >= rows * g16) return;
+  const long long row = t / g16;
+  const int c0 = int(t % g16) * 16;
+  uint4 r = make_uint4(~0u, ~0u, ~0u, ~0u);
+  const uint32_t thresh = dropout_threshold8(p);
+  if (p > 0.f) r = dropout_bits(rng[0], rng[1], stream, (unsigned long long)t);
+  const uint32_t w[4] = {r.x, r.y, r.z, r.w};
+  for (int e = 0; e < 16 && c0 + e < cols; ++e)
+    mask[row * cols + c0 + e] = (((w[e >> 2] >> ((e & 3) * 8)) & 0xFFu) >= thresh) ? 1 : 0;
+}
+
 // ------------------------------------------------------------------------------------------------ cast
 __global__ void cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n8) {
   const long long i = blockIdx.x * (long long)blockDim.x + threadIdx.x;
@@ -422,6 +438,14 @@ int b200_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned
   B200_REQUIRE(cols % 8 == 0, "dropout_mask: cols %% 8 != 0");
   const long long groups = (long long)rows * (cols / 8);
   dropout_mask_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(mask, groups, p, rng, rs);
+  B200_CHECK_CUDA(cudaGetLastError());
+  return 0;
+}
+
+int b200_attn_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned long long* rng, unsigned int rs,
+                           void* stream) {
+  const long long groups = (long long)rows * ((cols + 15) / 16);
+  attn_dropout_mask_kernel<<<(unsigned)((groups + 255) / 256), 256, 0, STREAM(stream)>>>(mask, rows, cols, p, rng, rs);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }

@@ -20,8 +20,6 @@ EPI_BF16, EPI_F32, EPI_F32_ATOMIC, EPI_ROPE_BF16, EPI_RESID_DROPOUT, EPI_SWIGLU,
 launch_count = 0
 # route plain / fp32-accumulate GEMMs to the CTA-pair kernel (set False to A/B against the 1-CTA kernel)
 use_pair_kernel = True
-# which attention-forward kernel attn_fwd() launches (see its docstring)
-attn_fwd_impl = int(os.environ.get("B200_ATTN_FWD", "1"))
 
 
 class GemmArgs(C.Structure):
@@ -81,7 +79,7 @@ _SIGS = {
     "b200_swiglu_fwd": [_P, _P, _I, _I, _P],
     "b200_swiglu_bwd": [_P, _P, _P, _I, _I, _P],
     "b200_attn_fwd": [_P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
-    "b200_attn_fwd2": [_P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
+    "b200_attn_dropout_mask": [_P, _I, _I, _F, _P, _U, _P],
     "b200_attn_bwd": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _U, _P],
     "b200_attn_bwd_rope": [_P, _P, _P, _P, _P, _P, _P, _I, _I, _I, _F, _P, _U, _P, _P, _P],
     "b200_ce_fwd_bwd": [_P, _P, _P, _I, _I, _I, _F, _F, _P],
@@ -254,11 +252,15 @@ def swiglu_bwd(dact_bf16, gu_bf16, dgu_bf16):
 
 
 # ----------------------------------------------------------------------------------------------- attention
-def attn_fwd(qkv_bf16, out_bf16, lse, batch, seq, heads, dropout_p, rng_state, rng_stream, impl=None):
-    """impl 1: one CTA per SM, 16 softmax warps, double-buffered S/O/P.  impl 2: two CTAs per SM, 8 softmax warps,
-    single-buffered.  Default from ``attn_fwd_impl`` (env ``B200_ATTN_FWD``)."""
-    _call("b200_attn_fwd2" if (impl or attn_fwd_impl) == 2 else "b200_attn_fwd", qkv_bf16.data_ptr(), out_bf16.data_ptr(), lse.data_ptr(), batch, seq, heads, dropout_p,
+def attn_fwd(qkv_bf16, out_bf16, lse, batch, seq, heads, dropout_p, rng_state, rng_stream):
+    _call("b200_attn_fwd", qkv_bf16.data_ptr(), out_bf16.data_ptr(), lse.data_ptr(), batch, seq, heads, dropout_p,
           _ptr(rng_state), rng_stream, _stream())
+
+
+def attn_dropout_mask(mask_u8, p, rng_state, rng_stream):
+    """keep-mask ``[B*H*S, S]`` (uint8) exactly as the attention kernels draw it (tests / oracles)."""
+    rows, cols = mask_u8.shape
+    _call("b200_attn_dropout_mask", mask_u8.data_ptr(), rows, cols, p, _ptr(rng_state), rng_stream, _stream())
 
 
 def attn_bwd(qkv_bf16, out_bf16, dout_bf16, lse, dqkv_bf16, delta, dq_accum, batch, seq, heads, dropout_p, rng_state,

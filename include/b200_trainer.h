@@ -177,10 +177,12 @@ int b200_swiglu_bwd(const void* dact_bf16, const void* gu_bf16, void* dgu_bf16, 
  * transpose+contiguous copy at gpt.py:238 disappears); lse: [B, H, S] fp32. */
 int b200_attn_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int seq, int heads, float dropout_p,
                   const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
-/* Same operation, small-footprint kernel (97 KB smem, 256 TMEM columns, 320 threads) so that two CTAs are
- * resident per SM and interleave their softmax / MMA phases; results interchangeable with b200_attn_fwd. */
-int b200_attn_fwd2(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int seq, int heads, float dropout_p,
-                   const unsigned long long* rng_state, unsigned int rng_stream, void* stream);
+/* keep-mask (uint8, [rows = B*H*S, cols = S]) of the attention dropout for (p, rng_state, rng_stream), exactly
+ * as b200_attn_fwd / b200_attn_bwd draw it: one Philox call per 16 consecutive kv positions of a query row, 8-bit
+ * lanes, dropped when lane < round(p * 256) (p = 0.1 -> 26/256; the kernels rescale by the realised keep
+ * probability).  For tests / oracles. */
+int b200_attn_dropout_mask(uint8_t* mask, int rows, int cols, float p, const unsigned long long* rng_state,
+                           unsigned int rng_stream, void* stream);
 /* dqkv: [B*S, 3h] bf16.  delta: caller-provided scratch [B, H, S] fp32; dq_accum: caller-provided fp32
  * scratch [B*S, h], zeroed by the call. */
 int b200_attn_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16, const float* lse,

@@ -10,16 +10,19 @@ def _attn_mask(B, H, S, p, rng, stream):
     """keep-mask [B,H,S,S] exactly as the attention kernels draw it (groups of 8 along kv)."""
     from distributed_llm_trainer_b200.ops import kernels as k
 
-    S8 = (S + 7) // 8
-    m = torch.zeros(B * H * S, S8 * 8, dtype=torch.uint8, device="cuda")
-    k.dropout_mask(m, p, rng, stream)
-    return m[:, :S].reshape(B, H, S, S).float()
+    m = torch.zeros(B * H * S, S, dtype=torch.uint8, device="cuda")
+    k.attn_dropout_mask(m, p, rng, stream)
+    return m.reshape(B, H, S, S).float()
+
+
+def _p_eff(p):
+    """drop probability the kernels realise (8-bit lanes) and rescale by"""
+    return min(255, int(p * 256 + 0.5)) / 256.0
 
 
 @pytest.mark.parametrize("B,S,H,p", [(2, 128, 2, 0.0), (1, 512, 3, 0.0), (2, 384, 2, 0.1), (1, 200, 2, 0.1),
                                      (2, 1024, 4, 0.1)])
-@pytest.mark.parametrize("impl", [1, 2])
-def test_attention_fwd_bwd(B, S, H, p, impl):
+def test_attention_fwd_bwd(B, S, H, p):
     from distributed_llm_trainer_b200.ops import kernels as k
     from distributed_llm_trainer_b200.ops import reference as R
 
@@ -29,7 +32,7 @@ def test_attention_fwd_bwd(B, S, H, p, impl):
     rng = torch.tensor([42, 3], dtype=torch.int64, device="cuda")
     out = torch.zeros(B * S, h, device="cuda", dtype=torch.bfloat16)
     lse = torch.zeros(B, H, S, device="cuda")
-    k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9, impl=impl)
+    k.attn_fwd(qkv, out, lse, B, S, H, p, rng, 9)
     torch.cuda.synchronize()
 
     def split(t):
@@ -37,7 +40,7 @@ def test_attention_fwd_bwd(B, S, H, p, impl):
 
     q, kk, v = [x.clone().requires_grad_(True) for x in split(qkv)]
     mask = _attn_mask(B, H, S, p, rng, 9) if p > 0 else None
-    ref = R.causal_attention(q, kk, v, mask, p)                     # [B,H,S,D]
+    ref = R.causal_attention(q, kk, v, mask, _p_eff(p))                     # [B,H,S,D]
     ref_out = ref.permute(0, 2, 1, 3).reshape(B * S, h)
     err = (out.float() - ref_out).abs().max().item()
     assert err < 0.03, f"fwd err {err}"

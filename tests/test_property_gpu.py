@@ -123,7 +123,7 @@ def test_cross_entropy_any_shape(rows, vocab, pad):
 def test_attention_any_shape(b, s, h, p):
     from distributed_llm_trainer_b200.ops import kernels as k
     from distributed_llm_trainer_b200.ops import reference as R
-    from .test_attention_gpu import _attn_mask
+    from .test_attention_gpu import _attn_mask, _p_eff
 
     torch.manual_seed(b * 100 + s + h)
     hd = h * 64
@@ -135,7 +135,7 @@ def test_attention_any_shape(b, s, h, p):
     torch.cuda.synchronize()
     q, kk, v = [x.clone().requires_grad_(True) for x in qkv.float().reshape(b, s, 3, h, 64).permute(2, 0, 3, 1, 4)]
     mask = _attn_mask(b, h, s, p, rng, 4) if p > 0 else None
-    ref = R.causal_attention(q, kk, v, mask, p).permute(0, 2, 1, 3).reshape(b * s, hd)
+    ref = R.causal_attention(q, kk, v, mask, _p_eff(p)).permute(0, 2, 1, 3).reshape(b * s, hd)
     assert (out.float() - ref).abs().max().item() < 0.03
     dout = _bf((b * s, hd), 0.5)
     ref.backward(dout.float())
