@@ -1017,8 +1017,8 @@ unsigned long long b200_attn_bwd_noalloc_max_scratch_bytes(void) { return B200_A
 // Same result as b200_attn_bwd(); the caller passes inputs and outputs only.
 //
 //  * Size limit: batch*seq*heads*64*4 bytes (dQ accumulator) plus batch*heads*seq*4 bytes (row sums), each
-//    rounded up to 256, must fit in 32 MiB -- e.g. 8 x 1024 tokens at 12 heads (25.6 MiB) fits, 16 x 1024
-//    does not.  Larger problems are refused with an error; nothing is launched.
+//    rounded up to 256, must fit in 32 MiB, i.e. batch*seq*heads <= 129,055 -- 8 x 1024 tokens at 12 heads need 24.4 MiB and fit
+//    (the cap at 12 heads is 10,754 tokens), 16 x 1024 do not.  Larger problems are refused with an error; nothing is launched.
 //  * The first call on each device looks up the array's device address and raises the kernel's shared-memory
 //    limit.  Make that first call during start-up, before any stream capture begins.
 //  * All calls on a device share the one array and it still holds whatever the previous call left there.

@@ -81,6 +81,7 @@ struct Params {
   int ag_rank, ag_world;
   // ---- reduce-scatter fused into the epilogue (OWN instantiations): C's 128-row slabs belong to ranks ---------
   int own_world, own_slabs, own_rot;   // owner of slab s = ((s * world) / slabs + rot) % world
+  int n_fast;                          // tile order: n-tiles of a row block consecutive (see mtile/ntile)
   int own_prev;                        // tma_x = this rank's own accumulator: owner += acc + prev
 };
 
@@ -160,8 +161,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
   const int tiles_n = (p.N + BNP - 1) / BNP;
   // n-tile of linear tile index r (m fastest).  AG rotates the n order so locally owned weight rows come first.
+  // Rasterisation: m fastest by default (consecutive tiles share the B tile).  n_fast: the n-tiles of one row block
+  // are consecutive instead, so they run at the same time on neighbouring pairs and A -- when A is the operand
+  // that does not fit in L2 (LM-head dW: 416 MB of dlogits, three n-tiles) -- comes from HBM once, not per n-tile.
+  auto mtile = [&](int r) { return p.n_fast ? r / tiles_n : r % tiles_m; };
   auto ntile = [&](int r) {
-    int qn = r / tiles_m;
+    int qn = p.n_fast ? r % tiles_n : r / tiles_m;
     if constexpr (AG) {
       qn += p.ag_rot;
       if (qn >= tiles_n) qn -= tiles_n;
@@ -258,7 +263,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       for (int t = pair; t < num_tiles; t += npairs) {
         const int ks = t / tiles_mn;
         const int r = t - ks * tiles_mn;
-        const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;   // this CTA's rows
+        const int m0 = mtile(r) * 2 * BM + int(cta_rank) * BM;   // this CTA's rows
         const int nt = ntile(r) * BNP;
         // this CTA's half of the B tile; SwiGLU: leader stages gate rows, peer the matching up rows
         const int n0 = (EPI == EPI_SWIGLU) ? (cta_rank == 0 ? nt / 2 : p.half_n + nt / 2) : nt + int(cta_rank) * C::BNH;
@@ -377,7 +382,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       c = int(u - (long)it * kUnits);
       const int t = pair + it * npairs;
       const int r = t % tiles_mn;
-      m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
+      m0 = mtile(r) * 2 * BM + int(cta_rank) * BM;
       n0 = ntile(r) * BNP;
     };
     uint32_t g = 0;   // store-only staging ring position
@@ -453,7 +458,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     for (int it = 0; it < my_tiles; ++it) {
       const int t = pair + it * npairs;
       const int r = t % tiles_mn;
-      const int m0 = (r % tiles_m) * 2 * BM + int(cta_rank) * BM;
+      const int m0 = mtile(r) * 2 * BM + int(cta_rank) * BM;
       const int n0 = ntile(r) * BNP;
       const int row = m0 + r_in;
       const int buf = C::kAccBufs == 2 ? (it & 1) : 0;
@@ -874,6 +879,14 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, const b200
   p.rope_cos = a->rope_cos; p.rope_sin = a->rope_sin; p.seq_len = a->seq_len > 0 ? a->seq_len : 1; p.rope_cols = a->rope_cols;
   p.dropout_p = a->dropout_p; p.rng = a->rng_state; p.rng_stream = a->rng_stream; p.half_n = a->half_n;
 
+  {
+    // n-fastest order when A is too big for L2 (126 MB) while B fits easily and there are few n-tiles per row block
+    const double a_bytes = 2.0 * a->M * a->K, b_bytes = 2.0 * a->N * a->K;
+    const int tn = (a->N + bnp - 1) / bnp;
+    p.n_fast = (ag == nullptr && a_bytes > 96e6 && b_bytes < 48e6 && tn > 1 && tn <= 8) ? 1 : 0;
+    if (a->raster == 1) p.n_fast = 0;
+    if (a->raster == 2 && ag == nullptr) p.n_fast = 1;
+  }
   const long tiles = long((a->M + 2 * BM - 1) / (2 * BM)) * ((a->N + bnp - 1) / bnp) * p.split_k;
   int sms = sm_count();
   if (a->max_ctas > 0 && a->max_ctas < sms) sms = a->max_ctas;

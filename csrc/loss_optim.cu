@@ -92,25 +92,33 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict_
   float mx = block_reduce(fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])), scratch, true);
   constexpr float kLog2e = 1.4426950408889634f;
   const float neg_mxs = -mx * kLog2e;
-  // Pass 2: sum of exp (one FFMA + one MUFU per element).
+  // Pass 2: exponentials (one FFMA + one MUFU per element), summed in fp32 and written back over the staged row as
+  // bf16 -- the gradient pass then needs no second MUFU per element (2 x 4224 x 50k exps per chunk is ~100 us of
+  // the SFU pipes, as much as the kernel's HBM time).  The label's logit is picked up on the way.
+  __shared__ float s_xl;
+  const int lab_vec = int(label >> 3), lab_e = int(label & 7);
   float s4[4] = {0.f, 0.f, 0.f, 0.f};
   for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
     const uint4 q = srow[i];
     const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+    if (i == lab_vec) {
+      const float2 f = unpack_bf16x2(w[lab_e >> 1]);
+      s_xl = (lab_e & 1) ? f.y : f.x;
+    }
+    uint32_t o[4];
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const float2 f = unpack_bf16x2(w[e]);
-      s4[e] += ex2_approx_ftz(fmaf(f.x, kLog2e, neg_mxs)) + ex2_approx_ftz(fmaf(f.y, kLog2e, neg_mxs));
+      const float e0 = ex2_approx_ftz(fmaf(f.x, kLog2e, neg_mxs)), e1 = ex2_approx_ftz(fmaf(f.y, kLog2e, neg_mxs));
+      s4[e] += e0 + e1;
+      o[e] = pack_bf16x2(e0, e1);
     }
+    srow[i] = make_uint4(o[0], o[1], o[2], o[3]);
   }
   const float sum = block_reduce((s4[0] + s4[1]) + (s4[2] + s4[3]), scratch, false);
   const float inv = grad_scale / sum;
-  if (threadIdx.x == 0) {
-    const float xl = __bfloat162float(reinterpret_cast<const __nv_bfloat16*>(srow)[label]);
-    atomicAdd(loss_sum, (logf(sum) + mx - xl) * loss_scale);
-  }
+  if (threadIdx.x == 0) atomicAdd(loss_sum, (logf(sum) + mx - s_xl) * loss_scale);
   // Pass 3: gradient (softmax - onehot) * grad_scale, written over the logits.
-  const int lab_vec = int(label >> 3), lab_e = int(label & 7);
   for (int i = threadIdx.x; i < nvec; i += kCeThreads) {
     const uint4 q = srow[i];
     const uint32_t w[4] = {q.x, q.y, q.z, q.w};
@@ -118,8 +126,8 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict_
 #pragma unroll
     for (int e = 0; e < 4; ++e) {
       const float2 f = unpack_bf16x2(w[e]);
-      g[2 * e] = ex2_approx_ftz(fmaf(f.x, kLog2e, neg_mxs)) * inv;
-      g[2 * e + 1] = ex2_approx_ftz(fmaf(f.y, kLog2e, neg_mxs)) * inv;
+      g[2 * e] = f.x * inv;
+      g[2 * e + 1] = f.y * inv;
     }
     if (i == lab_vec) {
 #pragma unroll

@@ -241,7 +241,10 @@ class GPT(nn.Module):
         limit = self.config.max_seq_len
         for _ in range(max_new_tokens):
             window = input_ids if input_ids.size(1) <= limit else input_ids[:, -limit:]
-            logits, _ = self(window)
+            if self.resolved_backend() == "b200" and not torch.is_autocast_enabled():
+                logits = self.engine().forward_logits(window, last_only=True)   # only the last position's row of the head
+            else:
+                logits, _ = self(window)
             logits = logits[:, -1, :].float()
             if greedy or top_k == 1:
                 nxt = logits.argmax(dim=-1, keepdim=True)

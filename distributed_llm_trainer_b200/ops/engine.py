@@ -89,7 +89,6 @@ class _Workspace:
         self.loss_sum = torch.zeros(1, dtype=f32, device=dev)
         if training:
             self.dxnf = torch.empty(M, h, dtype=bf, device=dev)
-            self.dxnf32 = torch.empty(M, h, dtype=f32, device=dev)
             self.dx = torch.empty(M, h, dtype=f32, device=dev)
             self.dy = torch.empty(M, h, dtype=bf, device=dev)
             self.dxn = torch.empty(M, h, dtype=bf, device=dev)
@@ -101,6 +100,7 @@ class _Workspace:
             self.dq_acc = torch.empty(M, h, dtype=f32, device=dev)
         self.graphs: Dict[tuple, tuple] = {}     # (loss_scale, max_ctas, hooked) -> (CUDAGraph, launches per replay)
         self.calls = 0
+        self.n_valid: Optional[int] = None       # number of non-ignored targets when the caller masks labels
 
     def acts_for(self, l: int) -> _LayerActs:
         return self.acts[l if len(self.acts) > 1 else 0]
@@ -187,6 +187,11 @@ class FusedGPTEngine:
         ws = self._ws.get(key)
         if ws is None:
             self._grow_rope(S)
+            if not training:
+                # inference shapes come and go (generation grows S by one per token): keep the two most recent
+                stale = [k for k in self._ws if not k[2]]
+                for k in stale[:-1]:
+                    del self._ws[k]
             ws = _Workspace(self, B, S, training)
             self._ws[key] = ws
         return ws
@@ -222,21 +227,6 @@ class FusedGPTEngine:
         if self.grad_mode not in ("rs", "rs1") or self.rs_router is None or key is None:
             return None
         return self.rs_router(key, (self.grad_mode == "rs") if prev is None else prev)
-
-    def _wave_split(self, tiles: int, k_blocks: int) -> int:
-        """Split-K factor for a reduce-add GEMM of ``tiles`` 256-row pair tiles: the one whose tiles x split
-        work units fill whole waves of CTA pairs best (1 % per extra split for the added reduce-add traffic;
-        every unit keeps at least 16 K blocks)."""
-        pairs = max(1, (self.max_ctas if 0 < self.max_ctas < self.sm_count else self.sm_count) // 2)
-        best, best_score = 1, -1.0
-        for s in range(1, 17):
-            if s > 1 and k_blocks // s < 16:
-                break
-            units = tiles * s
-            score = units / (((units + pairs - 1) // pairs) * pairs) - 0.01 * (s - 1)
-            if score > best_score + 1e-9:
-                best, best_score = s, score
-        return best
 
     def _weights(self, l: int) -> LayerWeights:
         return self.weights_hook(l) if self.weights_hook is not None else self.w_layers[l]
@@ -307,26 +297,22 @@ class FusedGPTEngine:
         """Chunked tied LM head + CE.  ``ws.loss_sum += loss_scale * mean CE``; with_grad also fills
         ``ws.dxnf`` and accumulates the head's share of the tied-embedding gradient."""
         M, V = ws.M, self.vocab
-        n_valid = ws.B * (ws.S - 1)
+        # trainers label every position (labels = input_ids): B*(S-1) targets.  GPT.forward(labels=...) callers may
+        # mask targets with -100; module_forward counts them (ws.n_valid) so the mean is over the real targets
+        n_valid = ws.n_valid if ws.n_valid is not None else ws.B * (ws.S - 1)
         scale = loss_scale / max(n_valid, 1)
         labels = ws.labels.view(-1)
         w = self._emb_weight()
-        if with_grad:
-            ws.dxnf32.zero_()
         for r0 in range(0, M, ws.lm_rows):
             r1 = min(M, r0 + ws.lm_rows)
             logits = ws.logits[: r1 - r0]
             K.gemm(ws.xnf[r0:r1], w, logits, tile_n=256, max_ctas=self.max_ctas, N=self.vocab_padded)
             K.ce_fwd_bwd(logits, labels[r0:r1], ws.loss_sum, V, scale, scale)
             if with_grad:
-                # dX chunk: [rows, V] x [V, h] has only rows/128 * h/256 output tiles (21 for 896 x 768) but a
-                # 50k-long contraction, so split K across the SMs and reduce in fp32 (cast to bf16 afterwards)
-                # The split that fills whole waves of CTA pairs wins (measured, benchmarks/bench_splitk.py:
-                # 4096 x 768 has 48 pair tiles on 74 pairs -- split 1: 250 us, split 3 (144 units, 1.95 waves): 199 us)
-                tiles = ((r1 - r0 + 255) // 256) * ((ws.dxnf32.shape[1] + 255) // 256)
-                split = self._wave_split(tiles, (V + 63) // 64)
-                K.gemm(logits, w, ws.dxnf32[r0:r1], b_mn=True, epilogue=K.EPI_F32_ATOMIC, split_k=split, tile_n=256,
-                       max_ctas=self.max_ctas, K=V)
+                # dX chunk: [rows, V] x [V, h], one pass over the 50k-long contraction per output tile, written as
+                # bf16 directly.  (Measured, benchmarks/bench_lmhead.py, 4224 rows: split-K 1 254.8 us, split-K 3 with
+                # the fp32 reduce-add epilogue 287.6 us -- and split 1 needs no zero-fill and no cast pass.)
+                K.gemm(logits, w, ws.dxnf[r0:r1], b_mn=True, tile_n=256, max_ctas=self.max_ctas, K=V)
                 # tied-embedding gradient: the first chunk of a "store" micro-step overwrites, the last chunk of an
                 # "rs" micro-step carries everything accumulated so far to the owners, the rest accumulate locally
                 first, final = r0 == 0, r1 == M
@@ -335,8 +321,6 @@ class FusedGPTEngine:
                 K.gemm(logits, ws.xnf[r0:r1], self.g_emb, a_mn=True, b_mn=True,
                        epilogue=K.EPI_F32 if (first and fresh and rs is None) else K.EPI_F32_ATOMIC, tile_n=256,
                        max_ctas=self.max_ctas, M=V, K=r1 - r0, rs=rs)
-        if with_grad:
-            K.cast_f32_bf16(ws.dxnf32, ws.dxnf)
 
     def _emb_weight(self) -> torch.Tensor:
         return self.w_emb
@@ -402,6 +386,7 @@ class FusedGPTEngine:
         scalar ``loss_scale * mean CE`` (no host sync).  ``labels`` are unshifted, as in the reference."""
         B, S = input_ids.shape
         ws = self.workspace(B, S, True)
+        ws.n_valid = None
         self._load_inputs(ws, input_ids, labels)
         ws.calls += 1
         # FSDP hooks allocate pool slots on the host and cannot be replayed; the DDP gradient hook only forks
@@ -455,9 +440,39 @@ class FusedGPTEngine:
         self._lm_head_loss(ws, 1.0, with_grad=False)
         return ws.loss_sum.clone()
 
+    def _check_labels(self, input_ids, labels, training: bool) -> None:
+        """Public-API label handling (F.cross_entropy semantics, reference gpt.py:449-453): -100 targets are ignored
+        and the loss is the mean over the remaining ones; a label >= vocab raises.  One host sync, on this path only."""
+        B, S = input_ids.shape
+        ws = self.workspace(B, S, training)
+        ws.n_valid = None
+        if labels is None:
+            return
+        tgt = labels[:, 1:]
+        stats = torch.stack([(tgt >= 0).sum(), tgt.max() if tgt.numel() else tgt.new_zeros(())]).tolist()
+        if stats[1] >= self.vocab:
+            raise IndexError(f"label {int(stats[1])} is out of range for vocab_size {self.vocab}")
+        if stats[0] != tgt.numel():
+            ws.n_valid = int(stats[0])
+
+    def _sync_with_module(self) -> None:
+        """``loss.backward()`` callers drive the model with stock torch code (``torch.optim.AdamW``,
+        ``optimizer.zero_grad()``, ``load_state_dict``), which only sees the fp32 master views: the bf16 compute copy
+        is refreshed whenever a parameter changed since the last sync, and dropped ``.grad`` tensors
+        (``zero_grad(set_to_none=True)``) are re-bound to the zeroed flat gradient buffer."""
+        st = self.store
+        versions = tuple(p._version for p in st.params)
+        if versions != getattr(self, "_param_versions", None):
+            st.refresh_shadow()
+            self._param_versions = versions
+        if st.grad is not None and any(p.grad is None for p in st.params):
+            st.grad.zero_()
+            st.rebind_grads()
+
     # ---- nn.Module-compatible entry (GPT.forward) ------------------------------------------------------------
     def module_forward(self, input_ids: torch.Tensor, labels: Optional[torch.Tensor]):
         training = self.model.training and torch.is_grad_enabled()
+        self._check_labels(input_ids, labels, training)
         if not training:
             logits = self.forward_logits(input_ids)
             loss = None
@@ -467,6 +482,7 @@ class FusedGPTEngine:
         if labels is None:
             raise NotImplementedError("training-mode forward on the fused engine returns the loss only; "
                                       "pass labels (logits are never materialised), or call model.eval()")
+        self._sync_with_module()
         loss = _EngineLoss.apply(self, input_ids, labels, *self.store.params)
         return None, loss
 

@@ -31,7 +31,7 @@ class GemmArgs(C.Structure):
         ("epilogue", C.c_int), ("split_k", C.c_int), ("tile_n", C.c_int), ("max_ctas", C.c_int),
         ("rope_cos", C.c_void_p), ("rope_sin", C.c_void_p), ("seq_len", C.c_int), ("rope_cols", C.c_int),
         ("residual", C.c_void_p), ("dropout_p", C.c_float), ("rng_state", C.c_void_p), ("rng_stream", C.c_uint),
-        ("aux", C.c_void_p), ("ld_aux", C.c_int), ("half_n", C.c_int),
+        ("aux", C.c_void_p), ("ld_aux", C.c_int), ("half_n", C.c_int), ("raster", C.c_int),
     ]
 
 
@@ -132,7 +132,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
          rope_cos=None, rope_sin=None, seq_len: int = 0, rope_cols: int = 0,
          residual=None, dropout_p: float = 0.0, rng_state=None, rng_stream: int = 0,
          aux=None, half_n: int = 0, M: Optional[int] = None, N: Optional[int] = None, K: Optional[int] = None,
-         pair: Optional[bool] = None, ag=None, rs=None) -> None:
+         pair: Optional[bool] = None, ag=None, rs=None, raster: int = 0) -> None:
     """``c = a @ b`` on tcgen05.  ``pair=True`` selects the CTA-pair kernel (``cta_group::2``, 256x256 tiles,
     TMA-store epilogue); ``None`` lets ``use_pair_kernel`` decide for the epilogues that kernel implements.
 
@@ -153,7 +153,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
         epilogue=epilogue, split_k=split_k, tile_n=tile_n, max_ctas=max_ctas,
         rope_cos=_ptr(rope_cos), rope_sin=_ptr(rope_sin), seq_len=seq_len, rope_cols=rope_cols,
         residual=_ptr(residual), dropout_p=dropout_p, rng_state=_ptr(rng_state), rng_stream=rng_stream,
-        aux=_ptr(aux), ld_aux=0 if aux is None else aux.stride(0), half_n=half_n,
+        aux=_ptr(aux), ld_aux=0 if aux is None else aux.stride(0), half_n=half_n, raster=raster,
     )
     if ag is not None:
         # all-gather fused into the GEMM: ``b`` is the local gathered destination the kernel fills while it multiplies

@@ -92,17 +92,40 @@ class SignalPads:
 
     The counter lives in device memory and is bumped by the pad kernels themselves, so barrier /
     scalar-all-reduce launches carry no changing host argument and can sit inside a captured CUDA graph.
-    Invariant: all ranks issue the same sequence of pad operations, and never on two streams at once."""
+    Invariant: all ranks issue the same sequence of pad operations, and never two of them in flight at once.
+    The second half is enforced here: a pad operation issued on a different stream than the previous one is
+    ordered behind it with an event (two concurrent ones would both bump the epoch counter and deadlock every
+    rank until the 20 s device-side timeout); inside a stream capture the check raises instead."""
 
     def __init__(self, device: torch.device, group=None):
         nbytes = _lib.lib().b200_comm_pad_bytes()
         self.buf = SymmetricBuffer(nbytes // 4, torch.int32, device, group)
         self.rank, self.world = self.buf.rank, self.buf.world
         self.counter = torch.zeros(1, dtype=torch.int32, device=device)
+        self._last_stream: Optional[int] = None
+        self._last_event: Optional[torch.cuda.Event] = None
+
+    def _serialize(self) -> None:
+        cur = torch.cuda.current_stream()
+        if self._last_stream is not None and self._last_stream != cur.cuda_stream:
+            if torch.cuda.is_current_stream_capturing():
+                raise RuntimeError("SignalPads: pad operation captured on a different stream than the previous one")
+            if self._last_event is not None:
+                cur.wait_event(self._last_event)
+        self._last_stream = cur.cuda_stream
+
+    def _mark(self) -> None:
+        if not torch.cuda.is_current_stream_capturing():
+            self._last_event = torch.cuda.Event()
+            self._last_event.record(torch.cuda.current_stream())
 
     def barrier(self) -> None:
         """Device-side barrier on the current stream (no host sync)."""
+        self._serialize()
         K.comm_barrier(self.buf.ptrs, self.rank, self.world, self.counter)
+        self._mark()
 
     def allreduce_scalars(self, inp: torch.Tensor, out: torch.Tensor, n: int) -> None:
+        self._serialize()
         K.allreduce_scalars(self.buf.ptrs, self.rank, self.world, self.counter, inp, out, n)
+        self._mark()

@@ -72,6 +72,9 @@ typedef struct b200_gemm_args {
   void* aux;
   int ld_aux;
   int half_n;
+  /* pair kernel tile order: 0 = automatic, 1 = m fastest (neighbouring tiles share B), 2 = n fastest (the n-tiles
+     of a row block run together: A streams from HBM once when it does not fit in L2) */
+  int raster;
 } b200_gemm_args;
 
 /* Reference ops G3/G6/G8/G9 (gpt.py:185-187,239,278-281,447) and their backward GEMMs. */
