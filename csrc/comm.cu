@@ -325,9 +325,15 @@ sumsq_chunks_kernel(const float* __restrict__ grad, const Chunk* __restrict__ ch
 
 // AdamW over the chunks; the bf16 result goes to rank `dst`'s parameter buffer (or to every rank's), and the
 // gradient is cleared in the same pass (zero_grad) so the next step's reduce-adds start from zero.
+// one store, replicated by the NVSwitch into every rank's copy of the buffer (NVLS multicast mapping)
+__device__ __forceinline__ void multimem_st_bf16x4(void* mc_addr, uint2 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v2.bf16x2 [%0], {%1, %2};" ::"l"(mc_addr), "r"(v.x), "r"(v.y) : "memory");
+}
+
 __global__ void __launch_bounds__(256)
 adamw_chunks_kernel(float* __restrict__ master, float* __restrict__ grad, float* __restrict__ m, float* __restrict__ v,
-                    PeerTable shadows, int world, int rank, const uint8_t* __restrict__ decay_chunks,
+                    PeerTable shadows, __nv_bfloat16* __restrict__ mc_base, int world, int rank,
+                    const uint8_t* __restrict__ decay_chunks,
                     const Chunk* __restrict__ ch, int nch, float lr, float beta1, float beta2, float eps, float wd,
                     float step_size, float inv_sqrt_bc2, const float* __restrict__ grad_scale, int zero_grad) {
   const float gs = grad_scale ? *grad_scale : 1.f;
@@ -358,6 +364,8 @@ adamw_chunks_kernel(float* __restrict__ master, float* __restrict__ grad, float*
       const uint2 s = make_uint2(pack_bf16x2(pp[0], pp[1]), pack_bf16x2(pp[2], pp[3]));
       if (k.dst >= 0) {
         *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(shadows.p[k.dst]) + k.sh + e) = s;
+      } else if (mc_base != nullptr) {
+        multimem_st_bf16x4(mc_base + k.sh + e, s);   // NVLS: 2 B/param leave this GPU once, not world - 1 times
       } else {
         for (int r = 0; r < world; ++r)
           *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(shadows.p[(rank + r) % world]) + k.sh + e) = s;
@@ -390,19 +398,41 @@ cast_scatter_chunks_kernel(const float* __restrict__ master, float* __restrict__
 
 // Small tensors (norm weights) accumulate in every rank's own buffer; their owner pulls the peers' copies:
 // dst[pg ..] = sum_r src_r[g ..], and every rank's copy is cleared for the next step (zero_remote).
+__device__ __forceinline__ float4 multimem_ld_reduce_add_f32x4(const float* mc_addr) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0, %1, %2, %3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc_addr) : "memory");
+  return v;
+}
+__device__ __forceinline__ void multimem_st_f32x4(float* mc_addr, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc_addr), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w) : "memory");
+}
+
+// mc_src != NULL (NVLS multicast address of the same symmetric buffer): the sum over ranks is ONE
+// multimem.ld_reduce -- the NVSwitch adds the ranks' copies and returns the result -- and one multimem.st of zeros
+// clears every copy, instead of world loads and world stores per element.
 __global__ void __launch_bounds__(256)
-pull_reduce_chunks_kernel(PeerTable srcs, float* __restrict__ dst, const Chunk* __restrict__ ch, int nch, int rank,
-                          int world, int zero_remote) {
+pull_reduce_chunks_kernel(PeerTable srcs, float* __restrict__ mc_src, float* __restrict__ dst,
+                          const Chunk* __restrict__ ch, int nch, int rank, int world, int zero_remote) {
   for (int c = blockIdx.x; c < nch; c += gridDim.x) {
     const Chunk k = ch[c];
     for (int i = threadIdx.x; i < (k.n >> 2); i += 256) {
       const long long e = 4LL * i;
       float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
-      for (int r = 0; r < world; ++r) {
-        float* src = reinterpret_cast<float*>(srcs.p[(rank + r) % world]) + k.g + e;
-        const float4 a = ld_peer_f4(src);
-        s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
-        if (zero_remote) *reinterpret_cast<float4*>(src) = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (mc_src != nullptr) {
+        s = multimem_ld_reduce_add_f32x4(mc_src + k.g + e);
+        if (zero_remote) {
+          __threadfence_system();   // the reduction has read every copy before the zeros go out (tiny tensors: cheap)
+          multimem_st_f32x4(mc_src + k.g + e, make_float4(0.f, 0.f, 0.f, 0.f));
+        }
+      } else {
+        for (int r = 0; r < world; ++r) {
+          float* src = reinterpret_cast<float*>(srcs.p[(rank + r) % world]) + k.g + e;
+          const float4 a = ld_peer_f4(src);
+          s.x += a.x; s.y += a.y; s.z += a.z; s.w += a.w;
+          if (zero_remote) *reinterpret_cast<float4*>(src) = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
       }
       *reinterpret_cast<float4*>(dst + k.pg + e) = s;   // last: dst may be this rank's own source
     }
@@ -574,7 +604,8 @@ int b200_sumsq_chunks(const float* grad, const b200_chunk* chunks_dev, int n_chu
 }
 
 int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg_sq, const void* const* param_ptrs,
-                      int rank, int world, const uint8_t* decay_chunks, const b200_chunk* chunks_dev, int n_chunks,
+                      void* param_multicast, int rank, int world, const uint8_t* decay_chunks,
+                      const b200_chunk* chunks_dev, int n_chunks,
                       int step, float lr, float beta1, float beta2, float eps, float weight_decay,
                       const float* grad_scale, int zero_grad, int max_ctas, void* stream) {
   if (n_chunks <= 0) return 0;
@@ -584,7 +615,9 @@ int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg
   const double bc2 = 1.0 - pow((double)beta2, (double)step);
   int cap = max_ctas > 0 ? max_ctas : sm_count() * 8;
   int blocks = n_chunks < cap ? n_chunks : cap;
-  adamw_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(master, grad, exp_avg, exp_avg_sq, sh, world, rank, decay_chunks,
+  adamw_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(master, grad, exp_avg, exp_avg_sq, sh,
+                                                         reinterpret_cast<__nv_bfloat16*>(param_multicast), world, rank,
+                                                         decay_chunks,
                                                          reinterpret_cast<const Chunk*>(chunks_dev), n_chunks, lr, beta1,
                                                          beta2, eps, weight_decay, (float)(lr / bc1),
                                                          (float)(1.0 / sqrt(bc2)), grad_scale, zero_grad);
@@ -604,13 +637,14 @@ int b200_cast_scatter_chunks(const float* master, float* grad_to_zero, const voi
   return 0;
 }
 
-int b200_pull_reduce_chunks(const void* const* src_ptrs, float* dst, const b200_chunk* chunks_dev, int n_chunks,
-                            int rank, int world, int zero_remote, void* stream) {
+int b200_pull_reduce_chunks(const void* const* src_ptrs, void* src_multicast, float* dst, const b200_chunk* chunks_dev,
+                            int n_chunks, int rank, int world, int zero_remote, void* stream) {
   if (n_chunks <= 0) return 0;
   PeerTable srcs;
   if (int rc = fill_table(&srcs, src_ptrs, world)) return rc;
   int blocks = n_chunks < sm_count() * 2 ? n_chunks : sm_count() * 2;
-  pull_reduce_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(srcs, dst, reinterpret_cast<const Chunk*>(chunks_dev),
+  pull_reduce_chunks_kernel<<<blocks, 256, 0, STREAM(stream)>>>(srcs, reinterpret_cast<float*>(src_multicast), dst,
+                                                               reinterpret_cast<const Chunk*>(chunks_dev),
                                                                n_chunks, rank, world, zero_remote);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;

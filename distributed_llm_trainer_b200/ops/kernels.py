@@ -59,8 +59,8 @@ _P, _I, _F, _LL, _U = C.c_void_p, C.c_int, C.c_float, C.c_longlong, C.c_uint
 _SIGS = {
     "b200_gemm2_rs_bf16": [C.POINTER(GemmArgs), C.POINTER(RsArgs), _P],
     "b200_sumsq_chunks": [_P, _P, _I, _P, _F, _P],
-    "b200_adamw_chunks": [_P, _P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _F, _F, _F, _F, _F, _P, _I, _I, _P],
-    "b200_pull_reduce_chunks": [_P, _P, _P, _I, _I, _I, _I, _P],
+    "b200_adamw_chunks": [_P, _P, _P, _P, _P, _P, _I, _I, _P, _P, _I, _I, _F, _F, _F, _F, _F, _P, _I, _I, _P],
+    "b200_pull_reduce_chunks": [_P, _P, _P, _P, _I, _I, _I, _I, _P],
     "b200_cast_scatter_chunks": [_P, _P, _P, _I, _I, _P, _I, _P],
     "b200_embed_bwd_rs": [_P, _P, _P, _I, _I, _I, _I, _I, _P],
     "b200_gemm2_ag_bf16": [C.POINTER(GemmArgs), C.POINTER(AgArgs), _P],
@@ -363,9 +363,11 @@ def sumsq_chunks(grad_f32, table, n_chunks, out, sq_scale: float = 1.0):
 
 
 def adamw_chunks(master, grad, exp_avg, exp_avg_sq, param_ptrs, rank, world, decay_chunks, table, n_chunks, step, lr,
-                 beta1, beta2, eps, wd, grad_scale, zero_grad: bool = True, max_ctas: int = 0):
+                 beta1, beta2, eps, wd, grad_scale, zero_grad: bool = True, max_ctas: int = 0, multicast_ptr: int = 0):
+    """``multicast_ptr``: NVLS multicast address of the parameter buffer (``MulticastBuffer.mc_ptr``); chunks with
+    dst = -1 are then broadcast by one ``multimem.st`` instead of one store per rank."""
     _call("b200_adamw_chunks", master.data_ptr(), grad.data_ptr(), exp_avg.data_ptr(), exp_avg_sq.data_ptr(), param_ptrs,
-          rank, world, decay_chunks.data_ptr(), table.data_ptr(), n_chunks, step, lr, beta1, beta2, eps, wd,
+          multicast_ptr or None, rank, world, decay_chunks.data_ptr(), table.data_ptr(), n_chunks, step, lr, beta1, beta2, eps, wd,
           _ptr(grad_scale), int(zero_grad), max_ctas, _stream())
 
 
@@ -374,9 +376,9 @@ def cast_scatter_chunks(master, grad_to_zero, param_ptrs, rank, world, table, n_
           n_chunks, _stream())
 
 
-def pull_reduce_chunks(src_ptrs, dst_f32, table, n_chunks, rank, world, zero_remote: bool = True):
-    _call("b200_pull_reduce_chunks", src_ptrs, dst_f32.data_ptr(), table.data_ptr(), n_chunks, rank, world,
-          int(zero_remote), _stream())
+def pull_reduce_chunks(src_ptrs, dst_f32, table, n_chunks, rank, world, zero_remote: bool = True, multicast_ptr: int = 0):
+    _call("b200_pull_reduce_chunks", src_ptrs, multicast_ptr or None, dst_f32.data_ptr(), table.data_ptr(), n_chunks, rank,
+          world, int(zero_remote), _stream())
 
 
 def memcpy_async(dst_ptr: int, src_ptr: int, nbytes: int) -> None:

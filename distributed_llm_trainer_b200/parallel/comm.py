@@ -87,6 +87,58 @@ class SymmetricBuffer:
             self._own_ptr = 0
 
 
+class MulticastBuffer:
+    """Symmetric buffer that ALSO has an NVLS multicast mapping: one ``multimem.st`` to ``mc_ptr + offset`` is
+    replicated by the NVSwitch into every rank's copy (reference: the broadcast half of DDP's all-reduce,
+    ddp_trainer.py:167-172 -- here one store per element leaves the GPU instead of world-1).  The driver objects
+    (cuMemCreate / cuMulticastCreate / cuMulticastBindMem, handle exchange between the ranks' processes) come from
+    ``torch.distributed._symmetric_memory``; the kernels that use the mapping are ours (``csrc/comm.cu``).
+    Same surface as ``SymmetricBuffer``; ``available()`` says whether this process model can have one."""
+
+    @staticmethod
+    def available() -> bool:
+        import os
+
+        if os.environ.get("B200_NVLS", "1") == "0":
+            return False
+        try:
+            import torch.distributed._symmetric_memory as symm  # noqa: F401
+        except Exception:
+            return False
+        return True
+
+    def __init__(self, numel: int, dtype: torch.dtype, device: torch.device, group=None):
+        import torch.distributed._symmetric_memory as symm
+
+        self.group = group
+        self.rank = dist.get_rank(group)
+        self.world = dist.get_world_size(group)
+        self.numel, self.dtype, self.device = numel, dtype, device
+        self._t = symm.empty(numel, dtype=dtype, device=device)
+        g = group if group is not None else dist.group.WORLD
+        self._hdl = symm.rendezvous(self._t, g.group_name)
+        self.mc_ptr = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        if self.mc_ptr == 0:
+            raise RuntimeError("symmetric memory came without a multicast mapping")
+        self._t.zero_()
+        self.raw_ptrs = [int(p) for p in self._hdl.buffer_ptrs]
+        self.ptrs = K.ptr_array(self.raw_ptrs)
+        self.local = self._t
+        torch.cuda.synchronize()
+        dist.barrier(group=group)
+
+    def offset_ptrs(self, byte_offset: int):
+        return K.ptr_array([p + byte_offset for p in self.raw_ptrs])
+
+    def close(self) -> None:
+        torch.cuda.synchronize()
+        if dist.is_initialized() and self.world > 1:
+            dist.barrier(group=self.group)
+        self._hdl = None
+        self._t = None
+        self.local = None
+
+
 class SignalPads:
     """Per-rank flag area + the epoch counter of pad operations.
 

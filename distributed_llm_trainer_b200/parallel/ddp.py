@@ -198,7 +198,8 @@ class NVLinkGradSync:
         mark("barrier")
         table, n = self._pull_chunks
         red = self.red_buf.local
-        K.pull_reduce_chunks(self.grad_buf.ptrs, red, table, n, self.rank, self.world, zero_remote=True)
+        K.pull_reduce_chunks(self.grad_buf.ptrs, red, table, n, self.rank, self.world, zero_remote=True,
+                             multicast_ptr=getattr(self.grad_buf, "mc_ptr", 0))
         table, n = self._chunks
         mark("pull")
         K.sumsq_chunks(red, table, n, self.sumsq[0:1], 1.0)
@@ -210,7 +211,7 @@ class NVLinkGradSync:
         mark("allreduce+clip")
         K.adamw_chunks(st.master, red, opt.exp_avg, opt.exp_avg_sq, self.shadow_buf.ptrs, self.rank, self.world,
                        opt._decay, table, n, opt.step_count, lr, b1, b2, eps, wd, opt.grad_scale, zero_grad=True,
-                       max_ctas=self.max_ctas)
+                       max_ctas=self.max_ctas, multicast_ptr=getattr(self.shadow_buf, "mc_ptr", 0))
         mark("adamw")
         # all parameter stores have landed and every owned gradient is zero again: the next step may start
         self.pads.barrier()
@@ -252,6 +253,28 @@ class NVLinkGradSync:
             self.shadow_buf.local[: self.store.total].copy_(self.store.master)
 
 
+def symmetric_or_multicast(numel: int, dtype, dev):
+    """Peer-mapped buffer with an NVLS multicast mapping when the box offers one (``mc_ptr`` != 0: broadcasts and
+    sums over ranks become single ``multimem`` instructions executed by the NVSwitch), plain CUDA-IPC mapping
+    otherwise (``B200_NVLS=0`` forces it).  Every rank must take the same branch, so the outcome is agreed on."""
+    from .comm import MulticastBuffer, SymmetricBuffer
+
+    ok = MulticastBuffer.available()
+    buf = None
+    if ok:
+        try:
+            buf = MulticastBuffer(numel, dtype, dev)
+        except Exception:      # no multicast support for this process model: every rank fails the same way
+            buf = None
+    flag = torch.tensor([1 if buf is not None else 0], device=dev)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    if int(flag.item()) == 1:
+        return buf
+    if buf is not None:
+        buf.close()
+    return SymmetricBuffer(numel, dtype, dev)
+
+
 def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, seed: int = 0):
     """Create the fused engine; with >1 rank its gradient and shadow buffers are peer-mapped."""
     from ..ops.engine import FusedGPTEngine
@@ -264,9 +287,8 @@ def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, s
 
     named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
     _, _, total = plan_layout(named)
-    grad_buf = SymmetricBuffer(total, torch.float32, dev)
+    grad_buf, shadow_buf = symmetric_or_multicast(total, torch.float32, dev), symmetric_or_multicast(total, torch.bfloat16, dev)
     red_buf = SymmetricBuffer(total, torch.float32, dev)
-    shadow_buf = SymmetricBuffer(total, torch.bfloat16, dev)
     pads = SignalPads(dev)
     store = FlatParamStore(model, device=dev, grad_buffer=grad_buf.local, shadow_buffer=shadow_buf.local)
     # replicas must start identical (reference: DDP broadcasts rank 0's parameters)

@@ -192,7 +192,9 @@ class ShardedGPT:
         # crosses NVLink once (the reference reduce-scatters every micro-step, fsdp_trainer.py:369-384;
         # B200_FSDP_ACCUM_LOCAL=0 does the same here: every micro-step delivers to the owners).  Peer-mapped only so
         # that owners can pull the few norm-weight gradients.
-        self.acc_buf = SymmetricBuffer(st.total, torch.float32, dev)
+        from .ddp import symmetric_or_multicast
+
+        self.acc_buf = symmetric_or_multicast(st.total, torch.float32, dev)
         self.accum_local = os.environ.get("B200_FSDP_ACCUM_LOCAL", "1") != "0"
         # Parameter gathers run on their own stream, prefetched ahead of the compute walk.
         self.gather_stream = torch.cuda.Stream(device=dev)
@@ -599,7 +601,8 @@ class ShardedGPT:
         self.pads.barrier()
         red = self.red_buf.local
         table, n = self._pull_chunks
-        K.pull_reduce_chunks(self.acc_buf.ptrs, red, table, n, self.rank, self.world, zero_remote=True)
+        K.pull_reduce_chunks(self.acc_buf.ptrs, red, table, n, self.rank, self.world, zero_remote=True,
+                             multicast_ptr=getattr(self.acc_buf, "mc_ptr", 0))
         table, n = self._chunks
         K.sumsq_chunks(red, table, n, self.sumsq[0:1], 1.0)
         self.pads.allreduce_scalars(self.sumsq, self.sumsq_total, 1)

@@ -293,10 +293,13 @@ typedef struct b200_chunk {
 int b200_sumsq_chunks(const float* grad, const b200_chunk* chunks_dev, int n_chunks, float* out, float sq_scale,
                       void* stream);
 /* AdamW over the chunks; updated bf16 parameters are stored into rank dst's buffer (param_ptrs[dst] + sh) or into
- * every rank's (dst = -1); zero_grad != 0 clears the gradient in the same pass (reference: optimizer.step +
+ * every rank's (dst = -1) -- with param_multicast != NULL (the NVLS multicast address of the same symmetric buffer)
+ * by ONE multimem.st that the NVSwitch replicates, otherwise by world stores; zero_grad != 0 clears the gradient in
+ * the same pass (reference: optimizer.step +
  * zero_grad + the parameter half of the all-reduce / next all-gather, ddp_trainer.py:356, fsdp_trainer.py:391). */
 int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg_sq, const void* const* param_ptrs,
-                      int rank, int world, const uint8_t* decay_chunks, const b200_chunk* chunks_dev, int n_chunks,
+                      void* param_multicast, int rank, int world, const uint8_t* decay_chunks,
+                      const b200_chunk* chunks_dev, int n_chunks,
                       int step, float lr, float beta1, float beta2, float eps, float weight_decay,
                       const float* grad_scale, int zero_grad, int max_ctas, void* stream);
 /* The parameter half of b200_adamw_chunks alone: bf16(master[pg ..]) stored to the chunks' holders, and
@@ -305,9 +308,11 @@ int b200_adamw_chunks(float* master, float* grad, float* exp_avg, float* exp_avg
 int b200_cast_scatter_chunks(const float* master, float* grad_to_zero, const void* const* param_ptrs, int rank, int world,
                              const b200_chunk* chunks_dev, int n_chunks, void* stream);
 /* dst[pg ..] = sum_r src_r[g ..] over the chunks (small tensors that every rank accumulates locally);
- * zero_remote != 0 also clears every rank's source copy for the next step (dst may alias this rank's source). */
-int b200_pull_reduce_chunks(const void* const* src_ptrs, float* dst, const b200_chunk* chunks_dev, int n_chunks,
-                            int rank, int world, int zero_remote, void* stream);
+ * zero_remote != 0 also clears every rank's source copy for the next step (dst may alias this rank's source).
+ * src_multicast != NULL (NVLS multicast address of the source buffer): the sum is one multimem.ld_reduce done inside
+ * the NVSwitch and the clearing one multimem.st, instead of world loads / stores per element. */
+int b200_pull_reduce_chunks(const void* const* src_ptrs, void* src_multicast, float* dst, const b200_chunk* chunks_dev,
+                            int n_chunks, int rank, int world, int zero_remote, void* stream);
 /* b200_embed_bwd with owner-directed rows (same slab rule as b200_gemm2_rs_bf16 over `vocab` rows): owner_base[o]
  * points at the first embedding-gradient row rank o owns. */
 int b200_embed_bwd_rs(const int64_t* ids, const float* dx, const void* const* owner_base, int rows, int hidden,

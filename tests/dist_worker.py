@@ -364,6 +364,58 @@ def mode_rsgemm(tmp):
     pads.buf.close()
 
 
+def mode_nvls(tmp):
+    """NVLS multicast: the AdamW parameter broadcast as one multimem.st per element and the small-tensor sum over
+    ranks as one multimem.ld_reduce, against the per-rank store / load forms of the same kernels."""
+    from distributed_llm_trainer_b200.ops import kernels as K
+    from distributed_llm_trainer_b200.parallel.comm import MulticastBuffer, SignalPads
+
+    local = int(os.environ["LOCAL_RANK"])
+    dev = torch.device(f"cuda:{local}")
+    torch.cuda.set_device(dev)
+    dist.init_process_group("nccl", device_id=dev)
+    rank, world = dist.get_rank(), dist.get_world_size()
+    assert MulticastBuffer.available()
+    pads = SignalPads(dev)
+    n = 128 * 64 * world
+    sh = MulticastBuffer(n, torch.bfloat16, dev)
+    acc = MulticastBuffer(n, torch.float32, dev)
+    part = n // world
+    lo = rank * part
+    torch.manual_seed(5)                                  # same "model" everywhere; every rank updates its part
+    master = torch.randn(n, device=dev)
+    grad = torch.randn(n, device=dev)
+    m, v = torch.zeros(part, device=dev), torch.zeros(part, device=dev)
+    decay = torch.ones(n // 128, dtype=torch.uint8, device=dev)
+    scale = torch.ones(1, device=dev)
+    table, nch = K.make_chunk_table([(lo, lo, 0, lo, part, -1)], dev)
+    pads.barrier()
+    K.adamw_chunks(master, grad, m, v, sh.ptrs, rank, world, decay, table, nch, 1, 1e-2, 0.9, 0.95, 1e-8, 0.1, scale,
+                   zero_grad=False, multicast_ptr=sh.mc_ptr)
+    pads.barrier()
+    torch.cuda.synchronize()
+    mine = master[lo: lo + part].to(torch.bfloat16)
+    got = [torch.empty(part, dtype=torch.bfloat16, device=dev) for _ in range(world)]
+    dist.all_gather(got, mine)
+    assert torch.equal(sh.local, torch.cat(got)), "multimem.st broadcast: some rank's copy differs"
+    # sum over ranks inside the switch + clearing every copy
+    torch.manual_seed(100 + rank)
+    acc.local.copy_(torch.randn(n, device=dev))
+    want = acc.local.clone()
+    dist.all_reduce(want)
+    dst = torch.zeros(n, device=dev)
+    pads.barrier()
+    K.pull_reduce_chunks(acc.ptrs, dst, table, nch, rank, world, zero_remote=True, multicast_ptr=acc.mc_ptr)
+    pads.barrier()
+    torch.cuda.synchronize()
+    close(dst[lo: lo + part], want[lo: lo + part], 1e-5, "multimem.ld_reduce")
+    assert torch.all(acc.local == 0), "multimem.st of zeros did not clear this rank's copy"
+    dist.barrier()
+    sh.close()
+    acc.close()
+    pads.buf.close()
+
+
 def main():
     mode = sys.argv[1]
     tmp = sys.argv[2] if len(sys.argv) > 2 else "/tmp/b200_dist_test"
@@ -373,6 +425,8 @@ def main():
         mode_ddp(tmp)
     elif mode == "rsgemm":
         mode_rsgemm(tmp)
+    elif mode == "nvls":
+        mode_nvls(tmp)
     elif mode.startswith("fsdp"):
         parts = mode.split(":")
         opt = parts[2] if len(parts) > 2 else ""
