@@ -123,9 +123,10 @@ def release(trainer) -> None:
 
     import torch
 
-    close = getattr(getattr(trainer, "grad_sync", None), "close", None)
-    if close is not None:
-        close()
+    for owner in ("grad_sync", "sharded"):
+        close = getattr(getattr(trainer, owner, None), "close", None)
+        if close is not None:
+            close()
     for k in list(vars(trainer)):
         setattr(trainer, k, None)
     gc.collect()

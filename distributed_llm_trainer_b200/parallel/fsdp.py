@@ -233,6 +233,14 @@ class ShardedGPT:
         torch.cuda.synchronize()
         dist.barrier()
 
+    def close(self) -> None:
+        """Collective: release the peer-mapped buffers (the object must not be used afterwards)."""
+        torch.cuda.synchronize()
+        self._graphs.clear()
+        self.engine.rs_router = None
+        for b in (self.acc_buf, self.red_buf, self.shard_bf16, self.pads.buf):
+            b.close()
+
     # ------------------------------------------------------------------------------------------ setup helpers
     def _refresh_shard_from_master(self) -> None:
         """Full fp32 parameters (materialised) -> this rank's fp32 master rows (owner layout) and its bf16 parameter

@@ -106,6 +106,9 @@ class DistributedTrainer:
         if self.is_main_process:
             print(f"Device: {self.device}")
             print(f"Mixed precision: {mp} (dtype: {self.dtype})")
+            if self.device.type == "cuda" and self.path == "torch":
+                print(f"Note: the hand-written sm_100a engine is bf16-only; {mp} runs the PyTorch path "
+                      f"(autocast + cuBLAS + NCCL, as the reference)")
 
     def _setup_model(self, model: Optional[GPT]) -> None:
         cfg = self.training_config

@@ -71,6 +71,9 @@ class FSDPTrainer:
             self.device = torch.device("cpu")
             self.compute_dtype = torch.float32
         self.path = "b200" if (self.device.type == "cuda" and self.compute_dtype == torch.bfloat16) else "torch"
+        if self.is_main_process and self.device.type == "cuda" and self.path == "torch":
+            print(f"Note: the hand-written sm_100a engine is bf16-only; mixed_precision={mp} runs the PyTorch path "
+                  f"(autocast + cuBLAS + torch.distributed collectives)")
 
     def _setup_model(self, model: Optional[GPT]) -> None:
         cfg, fc = self.training_config, self.fsdp_config
