@@ -2,8 +2,10 @@
 
     python benchmarks/sass_evidence.py
 
-Counts, per kernel, the SASS mnemonics that B200_PROFILING.md names as proof of a Blackwell-native kernel."""
+Counts, per kernel, the SASS mnemonics that B200_PROFILING.md names as proof of a Blackwell-native kernel, and writes
+the full disassembly of the hot / fused kernels to profiles/sass/<kernel>.sass.gz."""
 import collections
+import gzip
 import os
 import re
 import subprocess
@@ -11,7 +13,25 @@ import subprocess
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 LIB = os.path.join(ROOT, "distributed_llm_trainer_b200", "ops", "libb200trainer.so")
 PAT = re.compile(r"\b(UTC[A-Z]*MMA[A-Z0-9_.]*|LDTM[A-Z0-9_.]*|STTM[A-Z0-9_.]*|UTMALDG[A-Z0-9_.]*|UTMASTG[A-Z0-9_.]*|"
-                 r"UTMAREDG[A-Z0-9_.]*|UBLKCP[A-Z0-9_.]*|SYNCS[A-Z0-9_.]*|HMMA[A-Z0-9_.]*|FFMA2|FADD2|FMUL2)\b")
+                 r"UTMAREDG[A-Z0-9_.]*|UBLKCP[A-Z0-9_.]*|SYNCS[A-Z0-9_.]*|HMMA[A-Z0-9_.]*|LDGMC[A-Z0-9_.]*|FFMA2|FADD2|FMUL2)\b")
+
+# full listings: (file name, substring of the demangled name, substring that must also match or None)
+LISTINGS = [
+    ("gemm2_wgrad_reduce_scatter_256", "gemm2_kernel<256, 1, 1, 2, 0, 1>", None),
+    ("gemm2_wgrad_local_256", "gemm2_kernel<256, 1, 1, 2, 0, 0>", None),
+    ("gemm2_plain_bf16_256", "gemm2_kernel<256, 0, 0, 0, 0, 0>", None),
+    ("gemm2_rope_allgather_256", "gemm2_kernel<256, 0, 0, 3, 1, 0>", None),
+    ("gemm2_resid_dropout_384", "gemm2_kernel<384, 0, 0, 4, 0, 0>", None),
+    ("gemm2_swiglu_256", "gemm2_kernel<256, 0, 0, 5, 0, 0>", None),
+    ("gemm2_swiglu_bwd_256", "gemm2_kernel<256, 0, 1, 6, 0, 0>", None),
+    ("attn_fwd", "attn_fwd_kernel", None),
+    ("attn_bwd", "attn_bwd_kernel", None),
+    ("ce_fwd_bwd", "ce_fwd_bwd_kernel", None),
+    ("adamw_chunks_multimem", "adamw_chunks_kernel", None),
+    ("pull_reduce_chunks_multimem", "pull_reduce_chunks_kernel", None),
+    ("embed_bwd_rs", "embed_bwd_rs_kernel", None),
+    ("comm_barrier", "comm_barrier_kernel", None),
+]
 
 
 def main():
@@ -22,29 +42,39 @@ def main():
              "TMA / mbarrier mnemonics named in `B200_PROFILING.md` (`UTC*MMA` = tcgen05.mma, `LDTM` = tcgen05.ld,",
              "`UTMALDG` / `UTMASTG` / `UTMAREDG` = TMA tensor load / store / reduce-add, `UBLKCP` = bulk async copy,",
              "`SYNCS` = mbarrier ops, `F*2` = packed fp32 pairs).  `HMMA` (legacy mma.sync) appears nowhere.",
-             "Template arguments of `g2::gemm2_kernel` are <tile N, A MN-major, B MN-major, epilogue, fused all-gather>.\n",
-             "| kernel | tcgen05.mma | tcgen05.ld | TMA load | TMA store/reduce | bulk copy | mbarrier | packed fp32 | HMMA |",
+             "Template arguments of `g2::gemm2_kernel` are <tile N, A MN-major, B MN-major, epilogue, fused all-gather,",
+             "owner-directed (reduce-scatter) output>.  `LDGMC` = multimem.ld_reduce (NVLS); multimem.st disassembles as a",
+             "plain `STG...STRONG.SYS` to the multicast address.  Full listings of the hot / fused kernels: `profiles/sass/*.sass.gz`.\n",
+             "| kernel | tcgen05.mma | tcgen05.ld/st | TMA load | TMA store/reduce | bulk copy | mbarrier | packed fp32 | HMMA |",
              "|---|---|---|---|---|---|---|---|---|"]
     rows, hm_total = [], 0
+    os.makedirs(os.path.join(ROOT, "profiles", "sass"), exist_ok=True)
+    written = []
     for f in funcs:
         name = f.split("\n", 1)[0].strip()
         dem = subprocess.run(["cu++filt", name], capture_output=True, text=True).stdout.strip() or name
         dem = dem.replace("(bool)0", "0").replace("(bool)1", "1").replace("(int)", "")
         dem = re.sub(r"^void ", "", dem)
+        for fname, key, _ in LISTINGS:
+            if key in dem and fname not in written:
+                with gzip.open(os.path.join(ROOT, "profiles", "sass", fname + ".sass.gz"), "wt") as gz:
+                    gz.write("Function : " + dem + "\n" + f.split("\n", 1)[1])
+                written.append(fname)
         dem = re.sub(r"\((CUtensorMap|const |float|__nv|unsigned|long|b200::).*", "", dem)
         c = collections.Counter(m.group(1).split(".")[0] for m in PAT.finditer(f))
         mma = sum(v for k, v in c.items() if k.startswith("UTC") and "MMA" in k)
         hm_total += c.get("HMMA", 0)
-        if mma == 0 and c.get("UTMALDG", 0) == 0 and c.get("UBLKCP", 0) == 0:
+        if mma == 0 and c.get("UTMALDG", 0) == 0 and c.get("UBLKCP", 0) == 0 and c.get("LDGMC", 0) == 0:
             continue
-        rows.append(f"| `{dem[:80]}` | {mma} | {c.get('LDTM', 0)} | {c.get('UTMALDG', 0)} | "
+        rows.append(f"| `{dem[:80]}` | {mma} | {c.get('LDTM', 0)}/{c.get('STTM', 0)} | {c.get('UTMALDG', 0)} | "
                     f"{c.get('UTMASTG', 0) + c.get('UTMAREDG', 0)} | {c.get('UBLKCP', 0)} | {c.get('SYNCS', 0)} | "
                     f"{c.get('FFMA2', 0) + c.get('FADD2', 0) + c.get('FMUL2', 0)} | {c.get('HMMA', 0)} |")
     lines += sorted(rows)
-    lines.append(f"\nTotal `HMMA` instructions in the library: {hm_total}.")
+    lines.append(f"\nTotal `HMMA` instructions in the library: {hm_total}.  `LDGMC` (multimem.ld_reduce): "
+                 f"{len(re.findall(r'LDGMC', txt))}.  Listings written: {', '.join(sorted(written))}.")
     ex = []
     for p in (r"(UTCHMMA[^;]*;)", r"(UTMALDG[^;]*;)", r"(UTMASTG[^;]*;)", r"(UTMAREDG[^;]*;)", r"(LDTM[^;]*;)",
-              r"(UBLKCP[^;]*;)", r"(FFMA2[^;]*;)"):
+              r"(UBLKCP[^;]*;)", r"(FFMA2[^;]*;)", r"(STTM[^;]*;)", r"(LDGMC[^;]*;)"):
         m = re.search(p, txt)
         if m:
             ex.append(m.group(1))

@@ -105,8 +105,7 @@ struct FwdSmem {
   static constexpr int kQ = 0;                     // 2 buffers (next tile's Q lands while this one finishes)
   static constexpr int kK = kQ + 2 * kTile;        // 2 stages
   static constexpr int kV = kK + 2 * kTile;        // 2 stages
-  static constexpr int kP = kV + 2 * kTile;        // 2 buffers x 32 KB
-  static constexpr int kBars = kP + 2 * kPTile;
+  static constexpr int kBars = kV + 2 * kTile;     // (the probabilities never touch shared memory: they live in TMEM)
   static constexpr int kXchg = kBars + 256;                 // float [2][4][128] row-max exchange
   static constexpr int kXchgL = kXchg + 2 * 4 * 128 * 4;    // float [4][128] row-sum exchange (end of a tile)
   static constexpr int kTotal = kXchgL + 4 * 128 * 4 + 1024;
@@ -180,6 +179,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
   const uint32_t tmem = *tmem_ptr;
   const uint32_t tS[2] = {tmem + 0, tmem + 128};
   const uint32_t tO[2] = {tmem + 256, tmem + 320};
+  // P~ (bf16, two per 32-bit column: 64 columns per 128 kv positions) is written by the softmax threads with
+  // tcgen05.st and read by the P V MMA as its A operand straight from tensor memory
+  const uint32_t tP[2] = {tmem + 384, tmem + 448};
 
   // Every role walks the same tile list; `ti` counts this CTA's tiles (Q buffer / phase) and `G` its kv
   // blocks across tiles (K/V stages, S/P/O buffers and their phases), so no barrier is ever re-armed.
@@ -234,12 +236,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         mbar_wait(&v_full[st], ph);
         mbar_wait(&o_free[st], ph ^ 1);
         tc_fence_after();
-        const uint32_t p_addr = smem_u32(smem + FwdSmem::kP + st * kPTile);
         const uint32_t v_addr = smem_u32(smem + FwdSmem::kV + st * kTile);
 #pragma unroll
-        for (int t = 0; t < kBlk / 16; ++t)
-          umma_bf16_ss(tO[st], make_smem_desc_sw128(p_addr + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
-                       make_smem_desc_sw128(v_addr + t * 2048, kTile, 1024), idesc_o, t > 0);
+        for (int t = 0; t < kBlk / 16; ++t)   // A = P~ from TMEM: 16 kv positions = 8 packed columns per K step
+          umma_bf16_ts(tO[st], tP[st] + t * 8, make_smem_desc_sw128(v_addr + t * 2048, kTile, 1024), idesc_o, t > 0);
         tc_commit(&v_empty[st]);
         tc_commit(&o_full[st]);
       };
@@ -343,8 +343,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
         const float m_use = (mx == -INFINITY) ? 0.f : mx;   // m, m_use: running max of the RAW scores
         const float alpha = ex2_ftz((m - m_use) * kScale2);
         const float neg_msc = -m_use * kScale2;
-        // probabilities -> smem (bf16, dropout applied, unnormalised)
-        const uint32_t sub = smem_u32(smem + FwdSmem::kP + st * kPTile) + (qt >> 1) * kTile;
+        // probabilities -> TMEM (bf16 pairs, dropout applied, unnormalised)
         float2 l2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
         const float2 sc2 = make_float2(kScale2, kScale2), nm2 = make_float2(neg_msc, neg_msc);
 #pragma unroll
@@ -353,6 +352,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
           uint4 rb = make_uint4(0u, 0u, 0u, 0u);
           if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + g16 * 16) >> 4));
           const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
+          uint32_t pk8[8];
 #pragma unroll
           for (int hf = 0; hf < 2; ++hf) {
             const int gq = g16 * 2 + hf;
@@ -374,12 +374,14 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
               keep_masks_bf16x2(w[hf * 2 + 1], t4, lo, hi);
               pk[2] &= lo; pk[3] &= hi;
             }
-            st_shared_v4(swz(sub, r, (qt & 1) * 4 + gq), pk[0], pk[1], pk[2], pk[3]);
+#pragma unroll
+            for (int e = 0; e < 4; ++e) pk8[hf * 4 + e] = pk[e];
           }
+          tmem_st_32x32b_x8(tP[st] + lane_off + qt * 16 + g16 * 8, pk8);
         }
         l = l * alpha + ((l2[0].x + l2[0].y) + (l2[1].x + l2[1].y));
+        tmem_st_wait();
         tc_fence_before();
-        fence_proxy_async_smem();
         __syncwarp();
         if (lane == 0) {
           mbar_arrive(&p_ready[st]);
@@ -696,7 +698,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     const int r = qd * 32 + lane;
     const uint32_t lane_off = uint32_t(qd * 32) << 16;
     const bool drop = p.p_drop > 0.f;
-    const uint32_t thresh8 = dropout_threshold8(p.p_drop);   // 0 without dropout: every lane kept
+    const uint32_t t4 = dropout_threshold8(p.p_drop) * 0x01010101u;
     const float keep_prob = drop ? dropout_keep_prob8(p.p_drop) : 1.f;
     const float log2_inv_keep = -log2f(keep_prob);
     const float keep_scale = keep_prob * kScale;
@@ -785,7 +787,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           // one Philox call (sixteen 8-bit lanes) covers this half's 16 kv positions
           uint4 rb = make_uint4(0u, 0u, 0u, 0u);
           if (drop) rb = dropout_bits(seed, offs, p.rng_stream, grp_row + ((j * kBlk + qt * 32 + hh * 16) >> 4));
-          const uint32_t w[4] = {rb.x, rb.y, rb.z, rb.w};
+          // keep flags: bit 7 of every byte (four scores per word compared at once); all kept without dropout
+          const uint32_t cm[4] = {drop ? bytes_ge_bit7(rb.x, t4) : 0x80808080u, drop ? bytes_ge_bit7(rb.y, t4) : 0x80808080u,
+                                  drop ? bytes_ge_bit7(rb.z, t4) : 0x80808080u, drop ? bytes_ge_bit7(rb.w, t4) : 0x80808080u};
+          const uint32_t negc_bits = __float_as_uint(neg_c);
 #pragma unroll
           for (int g2 = 0; g2 < 2; ++g2) {
             const int g = hh * 2 + g2;
@@ -797,13 +802,17 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
               const float2 t = ffma2(make_float2(__uint_as_float(dv[g2 * 8 + e]), __uint_as_float(dv[g2 * 8 + e + 1])),
                                      make_float2(kScale, kScale), make_float2(neg_c, neg_c));
               const float qp0 = ex2_ftz(arg.x), qp1 = ex2_ftz(arg.y);
-              const uint32_t wb = w[g2 * 2 + (e >> 2)];                                        // bytes e%4, e%4+1
-              const bool k0 = ((wb >> ((e & 3) * 8)) & 0xFFu) >= thresh8, k1 = ((wb >> ((e & 3) * 8 + 8)) & 0xFFu) >= thresh8;
-              const float2 d2 = fmul2(make_float2(qp0, qp1), make_float2(k0 ? t.x : neg_c, k1 ? t.y : neg_c));
+              // selects as logic ops on 32-bit masks expanded from the keep bits (prmt sign-replicate)
+              const uint32_t cw = cm[g2 * 2 + (e >> 2)];
+              const uint32_t m0 = (e & 2) ? byte_sign_mask<2>(cw) : byte_sign_mask<0>(cw);
+              const uint32_t m1 = (e & 2) ? byte_sign_mask<3>(cw) : byte_sign_mask<1>(cw);
+              const float t0 = __uint_as_float((__float_as_uint(t.x) & m0) | (negc_bits & ~m0));
+              const float t1 = __uint_as_float((__float_as_uint(t.y) & m1) | (negc_bits & ~m1));
+              const float2 d2 = fmul2(make_float2(qp0, qp1), make_float2(t0, t1));
               ds[e] = d2.x;
               ds[e + 1] = d2.y;
-              pd[e] = k0 ? qp0 : 0.f;
-              pd[e + 1] = k1 ? qp1 : 0.f;
+              pd[e] = __uint_as_float(__float_as_uint(qp0) & m0);
+              pd[e + 1] = __uint_as_float(__float_as_uint(qp1) & m1);
             }
             const int cc = (qt & 1) * 4 + g;
             st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),

@@ -93,4 +93,12 @@ __device__ __forceinline__ void keep_masks_bf16x2(uint32_t w, uint32_t t4, uint3
   asm("prmt.b32 %0, %1, 0, 0xBBAA;" : "=r"(hi) : "r"(c));
 }
 
+// 32-bit all-ones / all-zeros mask from bit 7 of byte B of c (for selecting fp32 values with logic ops)
+template <int B>
+__device__ __forceinline__ uint32_t byte_sign_mask(uint32_t c) {
+  uint32_t m;
+  asm("prmt.b32 %0, %1, 0, %2;" : "=r"(m) : "r"(c), "n"(0x8888 + 0x1111 * B));
+  return m;
+}
+
 }  // namespace b200
