@@ -16,6 +16,24 @@ sys.path.insert(0, ROOT)
 from bench import GA, MICRO_BATCH, SEQ, barrier_sync, dist_info, max_over_ranks  # noqa: E402
 
 
+def nvlink_kib(index: int):
+    """(tx, rx) payload KiB summed over this GPU's NVLinks since boot (NVML field values 138 / 139), or None."""
+    try:
+        import pynvml as nv
+
+        nv.nvmlInit()
+        h = nv.nvmlDeviceGetHandleByIndex(index)
+        vals = nv.nvmlDeviceGetFieldValues(h, [(138, 0xFFFFFFFF), (139, 0xFFFFFFFF)])
+        out = []
+        for v in vals:
+            if v.nvmlReturn != 0:
+                return None
+            out.append(int(v.value.ullVal))
+        return tuple(out)
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--iters", type=int, default=10)
@@ -42,6 +60,7 @@ def main():
     micro = MICRO_BATCH
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
     t_micro, t_step = [], []
+    nv0 = nvlink_kib(local)
     phases = {}
     marks = []
     if sync is not None:
@@ -75,12 +94,22 @@ def main():
         t_step.append(ev[1].elapsed_time(ev[2]))
         for (_, a), (nm, b) in zip(marks, marks[1:]):
             phases.setdefault(nm, []).append(a.elapsed_time(b))
+    nv1 = nvlink_kib(local)
     t_micro.sort()
     t_step.sort()
     med_m = max_over_ranks(t_micro[len(t_micro) // 2], dev)
     med_s = max_over_ranks(t_step[len(t_step) // 2], dev)
     if rank == 0:
         print(json.dumps({"phases_ms_rank0_median": {k: sorted(v)[len(v) // 2] for k, v in phases.items()}}))
+        if nv0 and nv1:
+            owned = sum(b - a for a, b in sync.ranges) if sync is not None else 0
+            total = eng.store.total
+            print(json.dumps({"nvlink_MB_per_step_rank0": {"tx": (nv1[0] - nv0[0]) * 1024 / 1e6 / args.iters,
+                                                           "rx": (nv1[1] - nv0[1]) * 1024 / 1e6 / args.iters},
+                              "algorithmic_MB_per_step": {
+                                  "gradient_out_fp32": 4 * (total - owned) / 1e6, "gradient_in_fp32": 4 * owned * (world - 1) / 1e6,
+                                  "params_in_bf16": 2 * (total - owned) / 1e6,
+                                  "params_out_bf16_multicast": 2 * owned / 1e6 if world > 1 else 0}}))
         print(json.dumps({"n_gpus": world, "micro_steps_ms": med_m, "end_of_step_ms": med_s, "total_ms": med_m + med_s,
                           "owned_params": sum(b - a for a, b in sync.ranges) if sync is not None else eng.store.total}))
     import torch.distributed as dist
