@@ -32,7 +32,20 @@ constexpr int BK = 64;
 constexpr int UMMA_K = 16;
 constexpr int kAStage = BM * BK * 2;   // 16 KB
 constexpr int kEpiBuf = 128 * 128;     // staging slot: 128 rows x 128 B
-constexpr int kEpiWarps = 8;           // two per scheduler
+#ifndef B200_EPI_WARPS
+#define B200_EPI_WARPS 8
+#endif
+// Epilogue warps: two per scheduler; the warps of a lane quarter split a unit's columns kParts ways.  Going from one
+// to two warps per scheduler halved the fused epilogues' time in round 1; -DB200_EPI_WARPS=16 (four per scheduler)
+// measured no further gain in round 2 (SwiGLU 70.6 vs 69.6 us, SwiGLU' 62.3 vs 62.4, RoPE 37.9 vs 34.8), and an L2
+// prefetch of a tile's epilogue inputs made them slower (SwiGLU' 70.5 us): these epilogues are bound by the staging
+// ring's load -> compute -> store round trip per unit, not by issue slots.
+constexpr int kEpiWarps = B200_EPI_WARPS;
+static_assert(kEpiWarps == 8 || kEpiWarps == 16, "8 or 16 epilogue warps");
+constexpr int kParts = kEpiWarps / 4;  // column parts of a unit (one per warp of a lane quarter)
+constexpr int kCB = 64 / kParts;       // bf16 columns per thread in a 64-column unit
+constexpr int kCF = 32 / kParts;       // fp32 columns per thread in a 32-column unit
+constexpr int kCh = 8 / kParts;        // 16-byte chunks of a staging row per thread
 constexpr int kEpiThreads = kEpiWarps * 32;
 constexpr int kThreads = 64 + kEpiThreads;
 
@@ -119,12 +132,13 @@ __device__ __forceinline__ uint4 ld_shared_v4(uint32_t addr) {
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
   return v;
 }
-// two MUFU ops (EX2, RCP) and two FMA-pipe ops; exp2f() / __fdividef() add range checks the epilogue cannot afford
+// sigmoid(x) = 0.5 tanh(x / 2) + 0.5: ONE MUFU op (tanh.approx, max relative error 2^-11) and two FMA-pipe ops.  The
+// SwiGLU epilogues are bound by their own instruction stream (two epilogue warps per scheduler), and the SFU pipe
+// issues 16 results per clock per SM: ex2 + rcp cost twice the MUFU slots.
 __device__ __forceinline__ float sigmoid_f(float x) {
-  float e, r;
-  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(-1.4426950408889634f * x));
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
-  return r;
+  float t;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.5f * x));
+  return fmaf(t, 0.5f, 0.5f);
 }
 
 // tma_c: primary output.  tma_x: second tensor -- RESID_DROPOUT: residual (fp32, input); SWIGLU: act (bf16,
@@ -364,7 +378,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
     // Eight warps: warps e and e+4 share a TMEM lane quarter (row r_in) and split every unit's columns in
     // halves, so each scheduler has two epilogue warps to overlap tcgen05.ld / smem / MUFU latencies.
     const int q = warp & 3;
-    const int hf = (warp - 2) >> 2;                       // column half owned inside a unit
+    const int pt = (warp - 2) >> 2;                       // column part owned inside a unit (0 .. kParts-1)
     const int r_in = q * 32 + lane;                       // row within this CTA's 128 x BNP accumulator
     const int sw = r_in & 7;
     const bool epi_leader = threadIdx.x == 64;
@@ -401,12 +415,12 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
       }
       ++g;
     };
-    // this thread's 32 bf16 columns (fp32 bits in v) -> chunks hf*4 .. hf*4+3 of its staging row
-    auto put_bf16x32 = [&](uint32_t slot, const uint32_t* v) {
+    // this thread's kCB bf16 columns (fp32 bits in v) -> chunks pt*kCh .. of its staging row
+    auto put_bf16 = [&](uint32_t slot, const uint32_t* v) {
       const uint32_t row_addr = slot + r_in * 128;
 #pragma unroll
-      for (int cc = 0; cc < 4; ++cc)
-        st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4),
+      for (int cc = 0; cc < kCh; ++cc)
+        st_shared_v4_u32(row_addr + (((pt * kCh + cc) ^ sw) << 4),
                          pack_bf16x2(__uint_as_float(v[cc * 8 + 0]), __uint_as_float(v[cc * 8 + 1])),
                          pack_bf16x2(__uint_as_float(v[cc * 8 + 2]), __uint_as_float(v[cc * 8 + 3])),
                          pack_bf16x2(__uint_as_float(v[cc * 8 + 4]), __uint_as_float(v[cc * 8 + 5])),
@@ -471,23 +485,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
 #pragma unroll 1
         for (int c = 0; c < kUnits; ++c) {
           const uint32_t slot = stage_begin();
-          uint32_t v[32];
-          tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, v);
+          uint32_t v[kCB];
+          tmem_ld_cols<kCB>(t_row + c * 64 + pt * kCB, v);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
-          put_bf16x32(slot, v);
+          put_bf16(slot, v);
           stage_end(&tma_c, n0 + c * 64, m0, false);
         }
       } else if constexpr (EPI == EPI_ROPE_BF16) {
         // one unit = one head; column j (< 32) pairs with j + 32, so both halves are read and each thread
         // produces its own half.  cos/sin depend on the row only: cached in registers for the whole tile.
-        float cs[32], sn[32];
+        constexpr int kHalfParts = kParts / 2;
+        const int hcol = (pt % kHalfParts) * kCB;     // this thread's first column inside its half of the head
+        float cs[kCB], sn[kCB];
         {
           const int pos = (row < p.M ? row : 0) % p.seq_len;
-          const float4* c4 = reinterpret_cast<const float4*>(p.rope_cos + size_t(pos) * 32);
-          const float4* s4 = reinterpret_cast<const float4*>(p.rope_sin + size_t(pos) * 32);
+          const float4* c4 = reinterpret_cast<const float4*>(p.rope_cos + size_t(pos) * 32 + hcol);
+          const float4* s4 = reinterpret_cast<const float4*>(p.rope_sin + size_t(pos) * 32 + hcol);
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
+          for (int i = 0; i < kCB / 4; ++i) {
             const float4 a = c4[i], b = s4[i];
             cs[4 * i] = a.x; cs[4 * i + 1] = a.y; cs[4 * i + 2] = a.z; cs[4 * i + 3] = a.w;
             sn[4 * i] = b.x; sn[4 * i + 1] = b.y; sn[4 * i + 2] = b.z; sn[4 * i + 3] = b.w;
@@ -496,22 +512,22 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
 #pragma unroll 1
         for (int c = 0; c < kUnits; ++c) {
           const uint32_t slot = stage_begin();
-          uint32_t v[32];
+          uint32_t v[kCB];
           if (n0 + c * 64 < p.rope_cols) {
-            uint32_t w[32];
-            tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, v);          // own half
-            tmem_ld_32x32b_x32(t_row + c * 64 + (hf ^ 1) * 32, w);    // partner half
+            uint32_t w[kCB];
+            tmem_ld_cols<kCB>(t_row + c * 64 + pt * kCB, v);                  // own columns
+            tmem_ld_cols<kCB>(t_row + c * 64 + (pt ^ kHalfParts) * kCB, w);   // partner columns (j <-> j + 32)
             tmem_ld_wait();
-            const float sgn = hf == 0 ? -1.0f : 1.0f;   // first half: x1*c - x2*s ; second half: x2*c + x1*s
+            const float sgn = pt < kHalfParts ? -1.0f : 1.0f;   // first half: x1*c - x2*s ; second half: x2*c + x1*s
 #pragma unroll
-            for (int e = 0; e < 32; ++e)
+            for (int e = 0; e < kCB; ++e)
               v[e] = __float_as_uint(__uint_as_float(v[e]) * cs[e] + sgn * __uint_as_float(w[e]) * sn[e]);
           } else {
-            tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, v);
+            tmem_ld_cols<kCB>(t_row + c * 64 + pt * kCB, v);
             tmem_ld_wait();
           }
           if (c == kUnits - 1) release_tmem(buf);
-          put_bf16x32(slot, v);
+          put_bf16(slot, v);
           stage_end(&tma_c, n0 + c * 64, m0, false);
         }
       } else if constexpr (EPI == EPI_F32 || EPI == EPI_F32_ATOMIC) {
@@ -546,15 +562,15 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             } else {
               slot = stage_begin();
             }
-            uint32_t v[16];
-            tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
+            uint32_t v[kCF];
+            tmem_ld_cols<kCF>(t_row + c * 32 + pt * kCF, v);
             tmem_ld_wait();
             if (c == kUnits - 1) release_tmem(buf);
             const uint32_t row_addr = slot + r_in * 128;
             if (p.own_prev) mbar_wait(&ld_bar[u_glob % NB], uint32_t(u_glob / NB) & 1);
 #pragma unroll
-            for (int cc = 0; cc < 4; ++cc) {
-              const uint32_t addr = row_addr + (((hf * 4 + cc) ^ sw) << 4);
+            for (int cc = 0; cc < kCh; ++cc) {
+              const uint32_t addr = row_addr + (((pt * kCh + cc) ^ sw) << 4);
               if (add_prev) {
                 const uint4 q4 = ld_shared_v4(addr);
                 st_shared_v4_u32(addr, __float_as_uint(__uint_as_float(q4.x) + __uint_as_float(v[cc * 4 + 0])),
@@ -579,14 +595,14 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
 #pragma unroll 1
           for (int c = 0; c < kUnits; ++c) {
             const uint32_t slot = stage_begin();
-            uint32_t v[16];
-            tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
+            uint32_t v[kCF];
+            tmem_ld_cols<kCF>(t_row + c * 32 + pt * kCF, v);
             tmem_ld_wait();
             if (c == kUnits - 1) release_tmem(buf);
             const uint32_t row_addr = slot + r_in * 128;
 #pragma unroll
-            for (int cc = 0; cc < 4; ++cc)
-              st_shared_v4_u32(row_addr + (((hf * 4 + cc) ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
+            for (int cc = 0; cc < kCh; ++cc)
+              st_shared_v4_u32(row_addr + (((pt * kCh + cc) ^ sw) << 4), v[cc * 4 + 0], v[cc * 4 + 1], v[cc * 4 + 2], v[cc * 4 + 3]);
             stage_end(&tma_c, n0 + c * 32, m0, EPI == EPI_F32_ATOMIC);
           }
         }
@@ -605,25 +621,25 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             }
           }
           const uint32_t slot = epi_base + uint32_t(u_glob % NB) * kEpiBuf;
-          uint32_t v[16];
-          tmem_ld_32x32b_x16(t_row + c * 32 + hf * 16, v);
+          uint32_t v[kCF];
+          tmem_ld_cols<kCF>(t_row + c * 32 + pt * kCF, v);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
           mbar_wait(&ld_bar[u_glob % NB], uint32_t(u_glob / NB) & 1);
           const uint32_t row_addr = slot + r_in * 128;
           const int col0 = n0 + c * 32;
 #pragma unroll
-          for (int g8 = 0; g8 < 2; ++g8) {
+          for (int g8 = 0; g8 < kCF / 8; ++g8) {
             float a8[8];
 #pragma unroll
             for (int e = 0; e < 8; ++e) a8[e] = __uint_as_float(v[g8 * 8 + e]) * inv_keep;
             if (drop)   // compare + select per element straight off the Philox words (no bit-mask round trip)
-              dropout_zero8(dropout_bits(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + hf * 2 + g8)),
+              dropout_zero8(dropout_bits(seed, offs, p.rng_stream, (unsigned long long)row * (p.N / 8) + (col0 / 8 + pt * (kCF / 8) + g8)),
                             thresh << 16, a8);
 #pragma unroll
             for (int hlf = 0; hlf < 2; ++hlf) {
-              const int cl = g8 * 2 + hlf;                 // local 16-byte chunk (4 floats) of this thread's 16 columns
-              const uint32_t addr = row_addr + (((hf * 4 + cl) ^ sw) << 4);
+              const int cl = g8 * 2 + hlf;                 // local 16-byte chunk (4 floats) of this thread's columns
+              const uint32_t addr = row_addr + (((pt * kCh + cl) ^ sw) << 4);
               const uint4 rq = ld_shared_v4(addr);
               st_shared_v4_u32(addr, __float_as_uint(__uint_as_float(rq.x) + a8[hlf * 4 + 0]),
                                __float_as_uint(__uint_as_float(rq.y) + a8[hlf * 4 + 1]),
@@ -642,27 +658,27 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         // accumulator columns [0, BNP/2) = gate, [BNP/2, BNP) = up, for intermediate columns n0/2 ...
 #pragma unroll 1
         for (int c = 0; c < kUnits; ++c) {
-          uint32_t gv[32], uv[32];
-          tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, gv);
-          tmem_ld_32x32b_x32(t_row + BNP / 2 + c * 64 + hf * 32, uv);
+          uint32_t gv[kCB], uv[kCB];
+          tmem_ld_cols<kCB>(t_row + c * 64 + pt * kCB, gv);
+          tmem_ld_cols<kCB>(t_row + BNP / 2 + c * 64 + pt * kCB, uv);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
           const int icol = n0 / 2 + c * 64;   // intermediate column of this unit
           uint32_t slot = stage_begin();
-          put_bf16x32(slot, gv);
+          put_bf16(slot, gv);
           stage_end(&tma_c, icol, m0, false);
           slot = stage_begin();
-          put_bf16x32(slot, uv);
+          put_bf16(slot, uv);
           stage_end(&tma_c, p.half_n + icol, m0, false);
           // activation from the bf16-rounded gate / up so that backward recomputation is bit-identical
 #pragma unroll
-          for (int e = 0; e < 32; ++e) {
+          for (int e = 0; e < kCB; ++e) {
             const float ga = __bfloat162float(__float2bfloat16_rn(__uint_as_float(gv[e])));
             const float ua = __bfloat162float(__float2bfloat16_rn(__uint_as_float(uv[e])));
             gv[e] = __float_as_uint(ga * sigmoid_f(ga) * ua);
           }
           slot = stage_begin();
-          put_bf16x32(slot, gv);
+          put_bf16(slot, gv);
           stage_end(&tma_x, icol, m0, false);
         }
       } else {  // EPI_SWIGLU_BWD: acc = d_act; inputs gate/up via TMA; outputs [dgate | dup]
@@ -682,16 +698,16 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
               tma_load_2d(smem_epi + (2 * npr + 1) * kEpiBuf, &tma_x, &ld_bar[npr], p.half_n + pn0 + pc * 64, pm0);
             }
           }
-          uint32_t d[32];
-          tmem_ld_32x32b_x32(t_row + c * 64 + hf * 32, d);
+          uint32_t d[kCB];
+          tmem_ld_cols<kCB>(t_row + c * 64 + pt * kCB, d);
           tmem_ld_wait();
           if (c == kUnits - 1) release_tmem(buf);
           mbar_wait(&ld_bar[pr], uint32_t(u_glob / 3) & 1);
           const uint32_t g_row = epi_base + (2 * pr) * kEpiBuf + r_in * 128;
           const uint32_t u_row = g_row + kEpiBuf;
 #pragma unroll
-          for (int cc = 0; cc < 4; ++cc) {
-            const uint32_t off = (((hf * 4 + cc) ^ sw) << 4);
+          for (int cc = 0; cc < kCh; ++cc) {
+            const uint32_t off = (((pt * kCh + cc) ^ sw) << 4);
             const uint4 gq = ld_shared_v4(g_row + off), uq = ld_shared_v4(u_row + off);
             const uint32_t gw[4] = {gq.x, gq.y, gq.z, gq.w}, uw[4] = {uq.x, uq.y, uq.z, uq.w};
             uint32_t og[4], ou[4];
