@@ -89,6 +89,7 @@ struct Params {
   long long ag_b_off;          // element offset of B inside the unit
   unsigned int* ag_flags;      // local, one per 128-row block of B: == ag_epoch once the block has landed
   unsigned int ag_epoch;
+  const unsigned int* ag_epoch_ptr;   // when set, the epoch is read from device memory (CUDA-graph replays see a fresh one)
   int ag_pairs;                // CTA pairs that gather instead of multiplying
   int ag_rot;                  // n-tile rotation so tiles over locally owned rows are visited first
   int ag_rank, ag_world;
@@ -170,6 +171,10 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
   const bool leader = cta_rank == 0;
   // AG: the first ag_pairs pairs of the grid are gather CTAs (pair < 0 below); the rest multiply
   const int ag_pairs = AG ? p.ag_pairs : 0;
+  // epoch published into the per-block flags: a launch argument, or -- so that a captured launch can be replayed --
+  // a word in device memory that the caller bumps (stream-ordered) before every launch
+  uint32_t ag_epoch = 0;
+  if constexpr (AG) ag_epoch = p.ag_epoch_ptr != nullptr ? *reinterpret_cast<const volatile unsigned int*>(p.ag_epoch_ptr) : p.ag_epoch;
   const int pair = int(blockIdx.x >> 1) - ag_pairs, npairs = int(gridDim.x >> 1) - ag_pairs;
 
   const int tiles_m = (p.M + 2 * BM - 1) / (2 * BM);
@@ -266,7 +271,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
         G = Gbase + n;
         tma_store_wait<0>();        // every byte of this block has been written
         __threadfence();
-        st_release_gpu_u32(p.ag_flags + nb, p.ag_epoch);
+        st_release_gpu_u32(p.ag_flags + nb, ag_epoch);
       }
     }
   } else if (warp == 0) {
@@ -289,7 +294,7 @@ gemm2_kernel(const __grid_constant__ CUtensorMap tma_a, const __grid_constant__ 
             const unsigned int* flag = p.ag_flags + n0 / 128;
             const unsigned long long t0 = global_timer_ns();
             uint32_t spins = 0;
-            while (ld_acquire_gpu_u32(flag) != p.ag_epoch) {
+            while (ld_acquire_gpu_u32(flag) != ag_epoch) {
               if ((++spins & 0xFF) == 0 && global_timer_ns() - t0 > B200_WAIT_TIMEOUT_NS) {
                 printf("b200: fused all-gather GEMM timed out waiting for weight rows %d (block %d)\n", n0, blockIdx.x);
                 __trap();
@@ -927,7 +932,7 @@ static int run_gemm2(const b200_gemm_args* a, const b200_ag_args* ag, const b200
     if (tiles < gemm_pairs) gemm_pairs = tiles;
     for (int i = 0; i < 16; ++i) p.ag_src[i] = i < ag->world ? ag->shard_ptrs[i] : nullptr;
     p.ag_dst = const_cast<void*>(a->B);
-    p.ag_part = ag->part_elems; p.ag_b_off = ag->b_offset_elems; p.ag_flags = ag->flags; p.ag_epoch = ag->epoch;
+    p.ag_part = ag->part_elems; p.ag_b_off = ag->b_offset_elems; p.ag_flags = ag->flags; p.ag_epoch = ag->epoch; p.ag_epoch_ptr = ag->epoch_dev;
     p.ag_pairs = gp; p.ag_rank = ag->rank; p.ag_world = ag->world;
     // first n-tile that contains a locally owned weight row
     long long first_local = ag->rank * ag->part_elems - ag->b_offset_elems;

@@ -40,6 +40,7 @@ class AgArgs(C.Structure):
     _fields_ = [
         ("shard_ptrs", C.c_void_p), ("part_elems", C.c_longlong), ("b_offset_elems", C.c_longlong),
         ("flags", C.c_void_p), ("epoch", C.c_uint), ("rank", C.c_int), ("world", C.c_int), ("gather_pairs", C.c_int),
+        ("epoch_dev", C.c_void_p),
     ]
 
 
@@ -157,10 +158,13 @@ def gemm(a: torch.Tensor, b: torch.Tensor, c: torch.Tensor, *, a_mn: bool = Fals
     )
     if ag is not None:
         # all-gather fused into the GEMM: ``b`` is the local gathered destination the kernel fills while it multiplies
+        # ``epoch``: an int, or a device int64 tensor whose low 32 bits are the epoch (bumped by the caller with
+        # rng_advance before the launch: replayable from a CUDA graph)
         shard_ptrs, part_elems, b_offset_elems, flags, epoch, rank, world, gather_pairs = ag
+        epoch_dev = epoch.data_ptr() if isinstance(epoch, torch.Tensor) else None
         agargs = AgArgs(shard_ptrs=C.cast(shard_ptrs, C.c_void_p), part_elems=part_elems, b_offset_elems=b_offset_elems,
-                        flags=flags.data_ptr(), epoch=epoch & 0xFFFFFFFF, rank=rank, world=world,
-                        gather_pairs=gather_pairs)
+                        flags=flags.data_ptr(), epoch=0 if epoch_dev else (epoch & 0xFFFFFFFF), rank=rank, world=world,
+                        gather_pairs=gather_pairs, epoch_dev=epoch_dev)
         _call("b200_gemm2_ag_bf16", C.byref(args), C.byref(agargs), _stream())
         return
     if rs is not None:

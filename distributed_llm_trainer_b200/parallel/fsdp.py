@@ -212,13 +212,16 @@ class ShardedGPT:
         self._graphs: Dict[Tuple[int, int, float], Any] = {}
         self._plain_calls: Dict[Any, int] = {}
         # The fused all-gather GEMM is opt-in (B200_FSDP_FUSE_AG=1): a PREFETCHED gather hides completely under
-        # the previous block's compute, the fused one only under its own GEMM -- measured +7 ms / step on the
-        # 355M benchmark at 2 GPUs (profiles/fsdp_comm_breakdown.md).  It pays when nothing precedes the GEMM.
+        # the previous block's compute, the fused one only under its own GEMM.  Round 2 (graph-replayable, device-side
+        # epoch): 355M benchmark at 2 GPUs 161.2-163.5 ms without, 172.6 / 165.3 / 167.1 / 167.9 ms with 2 / 6 / 10 / 16
+        # gather pairs (profiles/fsdp_comm_breakdown.md) -- still 1-2 % behind, so it stays opt-in.
         self.fuse_ag = (os.environ.get("B200_FSDP_FUSE_AG", "0") != "0" and self.L > 0
                         and min(self.unit_part[1:]) >= 16384 and 3 * h >= 256)
-        self.ag_pairs = int(os.environ.get("B200_FSDP_AG_PAIRS", "2"))
+        self.ag_pairs = int(os.environ.get("B200_FSDP_AG_PAIRS", "6"))
         self._ag_flags = [torch.zeros((3 * h + 127) // 128, dtype=torch.int32, device=dev) for _ in self.gather_pool]
-        self._ag_epoch = 0
+        # per pool slot: {unused, epoch} as two int64 words; the fused all-gather GEMM reads the low half of word 1,
+        # bumped on the stream before every launch (device-side, so the launch replays from a CUDA graph)
+        self._ag_epoch_state = [torch.zeros(2, dtype=torch.int64, device=dev) for _ in self.gather_pool]
         # engine bound to hooks
         self.engine = FusedGPTEngine.__new__(FusedGPTEngine)
         self._init_engine(model, seed, LayerWeights)
@@ -443,8 +446,11 @@ class ShardedGPT:
             return None
         slot = ent[0]
         self._gathered[l] = (slot, ent[1], False)
-        self._ag_epoch += 1
-        return (self._unit_ptrs(1 + l), self.unit_part[1 + l], self.qkv_off, self._ag_flags[slot], self._ag_epoch,
+        from ..ops import kernels as K
+
+        K.rng_advance(self._ag_epoch_state[slot], 1)
+        return (self._unit_ptrs(1 + l), self.unit_part[1 + l], self.qkv_off, self._ag_flags[slot],
+                self._ag_epoch_state[slot][1:2],
                 self.rank, self.world, self.ag_pairs)
 
     def _acquire_slot(self, l: int) -> int:
@@ -533,7 +539,7 @@ class ShardedGPT:
                 cur.wait_event(self._params_ready)
             self._gather_unit(0, self.root_w)       # parameters only change at the optimizer step
             self._root_stale = False
-        if not (self.use_graphs and not self.fuse_ag):
+        if not self.use_graphs:
             self._micro_body(ws, loss_scale)
             return ws.loss_sum
         key = (B, S, float(loss_scale), e.grad_mode)

@@ -100,6 +100,8 @@ typedef struct b200_ag_args {
   unsigned int epoch;            /* value published per block: use a new one for every call that reuses flags */
   int rank, world;
   int gather_pairs;              /* 0 = default (4 pairs = 8 SMs) */
+  const unsigned int* epoch_dev; /* optional: device word holding the epoch (overrides `epoch`); bump it on the same
+                                    stream before every launch -- what makes the launch replayable from a CUDA graph */
 } b200_ag_args;
 int b200_gemm2_ag_bf16(const b200_gemm_args* args, const b200_ag_args* ag, void* stream);
 
