@@ -53,33 +53,62 @@ __global__ void embed_bwd_kernel(const int64_t* __restrict__ ids, const float* _
 }
 
 // ------------------------------------------------------------------------------------------------ RMSNorm
-// one warp per row, two reads of the row (the second hits L1).  hidden % 8 == 0.
-__global__ void rmsnorm_fwd_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w,
-                                   __nv_bfloat16* __restrict__ y, float* __restrict__ rstd, int rows, int hidden,
-                                   float eps) {
+// One warp per row.  NV = ceil(hidden / 256) > 0: the row is requested up front (2 NV float4 loads in flight per lane)
+// and stays in registers for the sum of squares and the scaling -- one read of x.  NV = 0: generic two-pass fallback
+// for rows wider than 2048 (the second read hits L1).  hidden % 8 == 0.
+template <int NV>
+__global__ void __launch_bounds__(256)
+rmsnorm_fwd_kernel(const float* __restrict__ x, const __nv_bfloat16* __restrict__ w, __nv_bfloat16* __restrict__ y,
+                   float* __restrict__ rstd, int rows, int hidden, float eps) {
   const int row = blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
   if (row >= rows) return;
   const float4* xr = reinterpret_cast<const float4*>(x + size_t(row) * hidden);
-  float ss = 0.f;
-  for (int i = lane_id(); i < hidden / 4; i += 32) {
-    const float4 v = xr[i];
-    ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
-  }
-  ss = warp_sum(ss);
-  const float r = rsqrtf(ss / float(hidden) + eps);
-  if (lane_id() == 0) rstd[row] = r;
   const uint4* wr = reinterpret_cast<const uint4*>(w);
   uint4* yr = reinterpret_cast<uint4*>(y + size_t(row) * hidden);
-  for (int i = lane_id(); i < hidden / 8; i += 32) {
-    const float4 a = xr[2 * i], b = xr[2 * i + 1];
-    const uint4 wq = wr[i];
+  const int nvec = hidden / 8, lane = lane_id();
+  auto scaled = [](const float4 a, const float4 b, const uint4 wq, float r) {
     const float2 w0 = unpack_bf16x2(wq.x), w1 = unpack_bf16x2(wq.y), w2 = unpack_bf16x2(wq.z), w3 = unpack_bf16x2(wq.w);
-    uint4 o;
-    o.x = pack_bf16x2(a.x * r * w0.x, a.y * r * w0.y);
-    o.y = pack_bf16x2(a.z * r * w1.x, a.w * r * w1.y);
-    o.z = pack_bf16x2(b.x * r * w2.x, b.y * r * w2.y);
-    o.w = pack_bf16x2(b.z * r * w3.x, b.w * r * w3.y);
-    yr[i] = o;
+    return make_uint4(pack_bf16x2(a.x * r * w0.x, a.y * r * w0.y), pack_bf16x2(a.z * r * w1.x, a.w * r * w1.y),
+                      pack_bf16x2(b.x * r * w2.x, b.y * r * w2.y), pack_bf16x2(b.z * r * w3.x, b.w * r * w3.y));
+  };
+  if constexpr (NV > 0) {
+    float4 xa[NV], xb[NV];
+    uint4 wq[NV];
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nvec) {
+        xa[k] = xr[2 * i];
+        xb[k] = xr[2 * i + 1];
+        wq[k] = wr[i];
+      } else {
+        xa[k] = xb[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+        wq[k] = make_uint4(0, 0, 0, 0);
+      }
+    }
+    float ss = 0.f;
+#pragma unroll
+    for (int k = 0; k < NV; ++k)
+      ss += (xa[k].x * xa[k].x + xa[k].y * xa[k].y) + (xa[k].z * xa[k].z + xa[k].w * xa[k].w) +
+            (xb[k].x * xb[k].x + xb[k].y * xb[k].y) + (xb[k].z * xb[k].z + xb[k].w * xb[k].w);
+    ss = warp_sum(ss);
+    const float r = rsqrtf(ss / float(hidden) + eps);
+    if (lane == 0) rstd[row] = r;
+#pragma unroll
+    for (int k = 0; k < NV; ++k) {
+      const int i = lane + 32 * k;
+      if (i < nvec) yr[i] = scaled(xa[k], xb[k], wq[k], r);
+    }
+  } else {
+    float ss = 0.f;
+    for (int i = lane; i < hidden / 4; i += 32) {
+      const float4 v = xr[i];
+      ss += v.x * v.x + v.y * v.y + v.z * v.z + v.w * v.w;
+    }
+    ss = warp_sum(ss);
+    const float r = rsqrtf(ss / float(hidden) + eps);
+    if (lane == 0) rstd[row] = r;
+    for (int i = lane; i < nvec; i += 32) yr[i] = scaled(xr[2 * i], xr[2 * i + 1], wr[i], r);
   }
 }
 
@@ -373,8 +402,21 @@ int b200_embed_bwd(const int64_t* ids, const float* dx, float* dw, int rows, int
 int b200_rmsnorm_fwd(const float* x, const void* w, void* y, float* rstd, int rows, int hidden, float eps,
                      void* stream) {
   B200_REQUIRE(hidden % 8 == 0, "rmsnorm: hidden %% 8 != 0");
-  rmsnorm_fwd_kernel<<<(rows + 7) / 8, 256, 0, STREAM(stream)>>>(x, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, rstd,
-                                                                  rows, hidden, eps);
+#define B200_NORM_FWD(NV)                                                                                          \
+  rmsnorm_fwd_kernel<NV><<<(rows + 7) / 8, 256, 0, STREAM(stream)>>>(x, (const __nv_bfloat16*)w, (__nv_bfloat16*)y, rstd, \
+                                                                      rows, hidden, eps)
+  switch ((hidden + 255) / 256) {
+    case 1: B200_NORM_FWD(1); break;
+    case 2: B200_NORM_FWD(2); break;
+    case 3: B200_NORM_FWD(3); break;
+    case 4: B200_NORM_FWD(4); break;
+    case 5: B200_NORM_FWD(5); break;
+    case 6: B200_NORM_FWD(6); break;
+    case 7: B200_NORM_FWD(7); break;
+    case 8: B200_NORM_FWD(8); break;
+    default: B200_NORM_FWD(0);
+  }
+#undef B200_NORM_FWD
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
