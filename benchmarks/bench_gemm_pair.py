@@ -44,9 +44,9 @@ def main():
         case(f"{tag} o wgrad", h, h, T, True, True, k.EPI_F32_ATOMIC, sp)
         case(f"{tag} gate|up wgrad", 2 * I, h, T, True, True, k.EPI_F32_ATOMIC, sp)
         case(f"{tag} down wgrad", h, I, T, True, True, k.EPI_F32_ATOMIC, sp)
-    case("lm head fwd", 896, 50304, 768, False, False)
-    case("lm head dX", 896, 768, 50304, False, True, k.EPI_F32_ATOMIC, (1, 8, 16, 24))
-    case("lm head dW", 50304, 768, 896, True, True, k.EPI_F32_ATOMIC, (1,))
+    case("lm head fwd (4224-row chunk)", 4224, 50304, 768, False, False)
+    case("lm head dX", 4224, 768, 50304, False, True)
+    case("lm head dW", 50304, 768, 4224, True, True, k.EPI_F32_ATOMIC, (1,))
     case("square 8192", 8192, 8192, 8192, False, False)
 
 

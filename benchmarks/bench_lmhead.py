@@ -38,7 +38,7 @@ report("softmax-CE (in place)", timeit(lambda: k.ce_fwd_bwd(logits, labels, loss
 logits.copy_(keep)
 k.ce_fwd_bwd(logits, labels, loss, V, 1e-4, 1e-4)
 for r in (1, 2):
-    for split in (1, 3):
+    for split in (1, 3, 4, 7, 10):
         report(f"dX GEMM split={split} raster={r}",
                timeit(lambda: k.gemm(logits, w, dx32, b_mn=True, epilogue=k.EPI_F32_ATOMIC, split_k=split, tile_n=256, K=V,
                                      raster=r)))
