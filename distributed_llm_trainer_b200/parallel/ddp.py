@@ -285,6 +285,9 @@ def build_engine_for_ddp(model, distributed: bool, rank: int, world_size: int, s
         return eng, None
     from .comm import SignalPads, SymmetricBuffer
 
+    if world_size > 8:
+        raise NotImplementedError("the NVLink engines address the ranks of ONE NVSwitch domain (<= 8 GPUs): the wgrad "
+                                  f"GEMM carries one tensor map per owner; got world_size={world_size}")
     named = [(n, p) for n, p in model.named_parameters() if p.requires_grad]
     _, _, total = plan_layout(named)
     grad_buf, shadow_buf = symmetric_or_multicast(total, torch.float32, dev), symmetric_or_multicast(total, torch.bfloat16, dev)

@@ -97,8 +97,8 @@ def interleave(per_rank):
 
 
 # ------------------------------------------------------------------------------------------------ modes
-def mode_ddp(tmp):
-    ga, steps = 2, 3
+def mode_ddp(tmp, ga=2):
+    steps = 3
     tcfg = TrainingConfig(batch_size=2, gradient_accumulation_steps=ga, max_steps=50, warmup_steps=2,
                           mixed_precision=MP, seed=0, backend=BACKEND, checkpoint_dir=tmp)
     tr = DistributedTrainer(GPTConfig(**CFG), tcfg)
@@ -423,6 +423,10 @@ def main():
     os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     if mode == "ddp":
         mode_ddp(tmp)
+    elif mode == "ddp:ga1":      # a step of ONE micro-step: nothing accumulated locally, the wgrads deliver directly
+        mode_ddp(tmp, ga=1)
+    elif mode == "ddp:ga3":      # store / add / deliver micro-steps all present
+        mode_ddp(tmp, ga=3)
     elif mode == "rsgemm":
         mode_rsgemm(tmp)
     elif mode == "nvls":

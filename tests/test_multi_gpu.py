@@ -26,7 +26,7 @@ def _torchrun(mode, tmp, nproc, port):
                                        ("fsdp:SHARD_GRAD_OP", 29714), ("fsdp:NO_SHARD", 29715),
                                        ("fsdp:FULL_SHARD:offload", 29716), ("rsgemm", 29717), ("aggemm", 29718),
                                        ("fsdp:FULL_SHARD:fuseag", 29719), ("fsdp:FULL_SHARD:smgather", 29720),
-                                       ("fsdp:FULL_SHARD:everymicro", 29721), ("fsdp:FULL_SHARD:nographs", 29722), ("nvls", 29723)])
+                                       ("fsdp:FULL_SHARD:everymicro", 29721), ("fsdp:FULL_SHARD:nographs", 29722), ("nvls", 29723), ("ddp:ga1", 29724), ("ddp:ga3", 29725)])
 def test_multi_gpu(mode, port, tmp_path):
     n = _ngpu()
     if n < 2:
