@@ -127,6 +127,9 @@ class ShardedGPT:
         from .comm import SignalPads, SymmetricBuffer
 
         assert strategy in ("FULL_SHARD", "SHARD_GRAD_OP")
+        if world > 8:
+            raise NotImplementedError("the NVLink engines address the ranks of ONE NVSwitch domain (<= 8 GPUs): the wgrad "
+                                      f"GEMM carries one tensor map per owner; got world_size={world}")
         self.strategy, self.rank, self.world = strategy, rank, world
         self.cpu_offload = cpu_offload
         dev = next(model.parameters()).device
