@@ -101,15 +101,15 @@ def main():
     cases.append(("attention bwd (+delta, dq cast)", L * MB, lambda: k.attn_bwd(qkv_s, out, dy, lse, dqkv, delta, dq, B, S, Hh, 0.1, rng, 9)))
 
     Vp = (V + 7) // 8 * 8
-    rows = 4096
+    rows = 4224
     emb, logits = bf(Vp, h), torch.zeros(rows, Vp, device="cuda", dtype=torch.bfloat16)
     xs = bf(rows, h)
     cases.append(("lm head fwd (chunk)", 2 * MB, lambda: k.gemm(xs, emb, logits, tile_n=256, N=Vp)))
     labels = torch.randint(0, V, (rows,), device="cuda")
     loss = torch.zeros(1, device="cuda")
     cases.append(("cross entropy fwd+bwd (chunk)", 2 * MB, lambda: k.ce_fwd_bwd(logits, labels, loss, V, 1.0, 1.0)))
-    dx32, gemb = torch.zeros(rows, h, device="cuda"), torch.zeros(Vp, h, device="cuda")
-    cases.append(("lm head dX (chunk)", 2 * MB, lambda: k.gemm(logits, emb, dx32, b_mn=True, epilogue=k.EPI_F32_ATOMIC, split_k=2, tile_n=256, K=V)))
+    dxb, gemb = torch.zeros(rows, h, device="cuda", dtype=torch.bfloat16), torch.zeros(Vp, h, device="cuda")
+    cases.append(("lm head dX (chunk)", 2 * MB, lambda: k.gemm(logits, emb, dxb, b_mn=True, tile_n=256, K=V)))
     cases.append(("lm head dW (chunk)", 2 * MB, lambda: k.gemm(logits, xs, gemb, a_mn=True, b_mn=True, epilogue=k.EPI_F32_ATOMIC, tile_n=256, M=V, K=rows)))
 
     xf, wln, y, rstd = torch.randn(T, h, device="cuda"), bf(h), torch.zeros(T, h, device="cuda", dtype=torch.bfloat16), torch.zeros(T, device="cuda")
