@@ -39,7 +39,9 @@ constexpr int kEpiBuf = 128 * 128;     // staging slot: 128 rows x 128 B
 // to two warps per scheduler halved the fused epilogues' time in round 1; -DB200_EPI_WARPS=16 (four per scheduler)
 // measured no further gain in round 2 (SwiGLU 70.6 vs 69.6 us, SwiGLU' 62.3 vs 62.4, RoPE 37.9 vs 34.8), and an L2
 // prefetch of a tile's epilogue inputs made them slower (SwiGLU' 70.5 us): these epilogues are bound by the staging
-// ring's load -> compute -> store round trip per unit, not by issue slots.
+// ring's load -> compute -> store round trip per unit, not by issue slots.  Trading one operand stage for a deeper
+// input prefetch (residual 4 units ahead, SwiGLU' 2) was slower as well (small down+resid 53.3 -> 60.4 us, SwiGLU'
+// 63.5 -> 68.5 us): the mainloop needs its 4-5 stages more than the epilogue needs the slots.
 constexpr int kEpiWarps = B200_EPI_WARPS;
 static_assert(kEpiWarps == 8 || kEpiWarps == 16, "8 or 16 epilogue warps");
 constexpr int kParts = kEpiWarps / 4;  // column parts of a unit (one per warp of a lane quarter)
