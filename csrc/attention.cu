@@ -20,9 +20,12 @@
 //              select on the Philox words -> bf16 P tile written to 128B-swizzled smem (A operand of P V)
 //              -> running O kept in registers: o = o * alpha + O_j (no TMEM rescale pass).
 // Backward work item = (kv block, head, batch) looping over q blocks i >= j; five MMAs per pair:
-//   S = Q K^T, dP = dO V^T, dV += P~^T dO, dK += dS^T Q, dQ_i = dS K  (dQ reduced with red.global.add.f32)
-// S / dP of pair i+1 are issued as soon as pair i's are in registers; P~ / dS (smem) and dQ (TMEM) are double
-// buffered so the other three MMAs of pair i run under the element-wise work of pair i+1.
+//   S = Q K^T, dP = dO V^T, dV += P~^T dO, dK += dS^T Q, dQ_i = dS K
+// S / dP of pair i+1 are issued as soon as pair i's are in registers; dS (smem) and dQ (TMEM) are double buffered
+// so the other three MMAs of pair i run under the element-wise work of pair i+1 (P~ has one buffer, released by
+// the dV MMA, which runs first; Q / dO have three stages because a stage is held until the pair's LAST MMAs).
+// dQ tiles leave through TMA reduce-add into the fp32 accumulator, staged in the pair's own dS buffer: the
+// red.global.add.v4 it replaces touched 32 lines per warp instruction and held the loop on its source registers.
 // P~ / dS tiles are written once to smem and consumed both K-major (dS K) and MN-major (P~^T dO,
 // dS^T Q) through different UMMA descriptors -- no transposes.
 //
@@ -536,10 +539,10 @@ __global__ void attn_dq_rope_kernel(const float* __restrict__ dq, __nv_bfloat16*
 struct BwdSmem {
   static constexpr int kK = 0;
   static constexpr int kV = kK + kTile;
-  static constexpr int kQ = kV + kTile;            // 2 stages
-  static constexpr int kdO = kQ + 2 * kTile;       // 2 stages
-  static constexpr int kP = kdO + 2 * kTile;       // 2 buffers x 32 KB
-  static constexpr int kdS = kP + 2 * kPTile;      // 2 buffers x 32 KB
+  static constexpr int kQ = kV + kTile;            // 3 stages: a stage is held until the pair's dK MMA has read it, and
+  static constexpr int kdO = kQ + 3 * kTile;       // 3 stages  with two the next-but-one load started a pair too late
+  static constexpr int kP = kdO + 3 * kTile;       // 1 buffer of 32 KB (freed by the dV MMA: p_free)
+  static constexpr int kdS = kP + kPTile;          // 2 buffers x 32 KB (also the staging of the dQ reduce-add)
   static constexpr int kBars = kdS + 2 * kPTile;
   static constexpr int kTotal = kBars + 256 + 1024;
 };
@@ -551,22 +554,23 @@ static_assert(BwdSmem::kTotal <= 227 * 1024, "backward smem exceeds the 227 KB p
 // those two counters, so nothing is re-initialised between tiles.
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                const AttnParams p) {
+                const __grid_constant__ CUtensorMap tm_dq, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::kBars);
   uint64_t* kv_full = bars;            // 1
   uint64_t* kv_empty = bars + 1;       // 1  every MMA of the tile has completed: K / V may be replaced
-  uint64_t* qdo_full = bars + 2;       // 2
-  uint64_t* qdo_empty = bars + 4;      // 2
-  uint64_t* sdp_full = bars + 6;       // 1
-  uint64_t* s_free = bars + 7;         // 1 (count = softmax warps)
-  uint64_t* pds_ready = bars + 8;      // 2 (count = softmax warps)
-  uint64_t* dq_full = bars + 10;       // 2
-  uint64_t* dq_free = bars + 12;       // 2 (count = softmax warps)
-  uint64_t* acc_full = bars + 14;      // 1
-  uint64_t* acc_free = bars + 15;      // 1 (count = softmax warps): dK / dV have been read out of TMEM
-  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 16);
+  uint64_t* qdo_full = bars + 2;       // 3
+  uint64_t* qdo_empty = bars + 5;      // 3
+  uint64_t* sdp_full = bars + 8;       // 1
+  uint64_t* s_free = bars + 9;         // 1 (count = softmax warps)
+  uint64_t* pds_ready = bars + 10;     // 2 (count = softmax warps)
+  uint64_t* dq_full = bars + 12;       // 2
+  uint64_t* dq_free = bars + 14;       // 2 (count = softmax warps)
+  uint64_t* acc_full = bars + 16;      // 1
+  uint64_t* acc_free = bars + 17;      // 1 (count = softmax warps): dK / dV have been read out of TMEM
+  uint64_t* p_free = bars + 18;        // 1  the dV MMA of the pair has read P~
+  uint32_t* tmem_ptr = reinterpret_cast<uint32_t*>(bars + 19);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int nq = (p.S + kBlk - 1) / kBlk;
@@ -578,12 +582,14 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   if (threadIdx.x == 0) {
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
+    tma_prefetch_desc(&tm_dq);
     mbar_init(kv_full, 1);
     mbar_init(kv_empty, 1);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < 3; ++i) {
       mbar_init(&qdo_full[i], 1);
       mbar_init(&qdo_empty[i], 1);
     }
+    mbar_init(p_free, 1);
     mbar_init(sdp_full, 1);
     mbar_init(s_free, kSoftmaxWarps);
     for (int i = 0; i < 2; ++i) {
@@ -616,8 +622,8 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tma_load_2d(smem + BwdSmem::kK, &tm_qkv, kv_full, h + hd * kD, row_base + j * kBlk);
         tma_load_2d(smem + BwdSmem::kV, &tm_qkv, kv_full, 2 * h + hd * kD, row_base + j * kBlk);
         for (int it = 0; it < nq - j; ++it, ++I) {
-          const int st = I & 1;
-          mbar_wait(&qdo_empty[st], ((I >> 1) & 1) ^ 1);
+          const int st = I % 3;
+          mbar_wait(&qdo_empty[st], ((I / 3) & 1) ^ 1);
           mbar_expect_tx(&qdo_full[st], 2 * kTile);
           tma_load_2d(smem + BwdSmem::kQ + st * kTile, &tm_qkv, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
           tma_load_2d(smem + BwdSmem::kdO + st * kTile, &tm_do, &qdo_full[st], hd * kD, row_base + (j + it) * kBlk);
@@ -635,10 +641,10 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       // S = Q K^T and dP = dO V^T of pair I (one TMEM buffer each; the element-wise warps free it as soon
       // as both are in registers, so the next pair's S / dP run under this pair's softmax).
       auto issue_sdp = [&](uint32_t I) {
-        const int st = I & 1;
+        const int st = I % 3;
         const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
         const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
-        mbar_wait(&qdo_full[st], (I >> 1) & 1);
+        mbar_wait(&qdo_full[st], (I / 3) & 1);
         mbar_wait(s_free, (I & 1) ^ 1);
         tc_fence_after();
 #pragma unroll
@@ -662,11 +668,12 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         mbar_wait(acc_free, (ti & 1) ^ 1);     // previous tile's dK / dV have left TMEM
         for (int it = 0; it < niter; ++it) {
           const uint32_t I = I0 + it;
-          const int st = I & 1;                 // Q/dO stage, P/dS buffer and dQ buffer of this pair
+          const int st = I & 1;                 // dS buffer and dQ buffer of this pair
+          const int qst = I % 3;                // its Q / dO stage
           const uint32_t use = (I >> 1) & 1;
-          const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + st * kTile);
-          const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + st * kTile);
-          const uint32_t pb = p_addr + st * kPTile, dsb = ds_addr + st * kPTile;
+          const uint32_t q_addr = smem_u32(smem + BwdSmem::kQ + qst * kTile);
+          const uint32_t do_addr = smem_u32(smem + BwdSmem::kdO + qst * kTile);
+          const uint32_t pb = p_addr, dsb = ds_addr + st * kPTile;
           if (it + 1 < niter) issue_sdp(I + 1);
           mbar_wait(&pds_ready[st], use);
           mbar_wait(&dq_free[st], use ^ 1);
@@ -675,6 +682,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           for (int t = 0; t < 8; ++t)  // dV += P~^T dO   (K = 128 q rows, 16 per step)
             umma_bf16_ss(tdV, make_smem_desc_sw128(pb + t * 2048, kTile, 1024),
                          make_smem_desc_sw128(do_addr + t * 2048, kTile, 1024), idesc_tt, (it > 0 || t > 0));
+          tc_commit(p_free);           // the single P~ buffer may be rewritten by the next pair
 #pragma unroll
           for (int t = 0; t < 8; ++t)  // dK += dS^T Q
             umma_bf16_ss(tdK, make_smem_desc_sw128(dsb + t * 2048, kTile, 1024),
@@ -683,7 +691,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
           for (int t = 0; t < 8; ++t)  // dQ_i = dS K     (K = 128 kv, 16 per step)
             umma_bf16_ss(tdQ + st * 64, make_smem_desc_sw128(dsb + (t >> 2) * kTile + (t & 3) * 32, 16, 1024),
                          make_smem_desc_sw128(k_addr + t * 2048, kTile, 1024), idesc_dq, t > 0);
-          tc_commit(&qdo_empty[st]);
+          tc_commit(&qdo_empty[qst]);
           tc_commit(&dq_full[st]);
         }
         tc_commit(acc_full);
@@ -706,6 +714,13 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     if (drop) { seed = p.rng[0]; offs = p.rng[1]; }
     const uint32_t p_sub0 = smem_u32(smem + BwdSmem::kP) + (qt >> 1) * kTile;
     const uint32_t ds_sub0 = smem_u32(smem + BwdSmem::kdS) + (qt >> 1) * kTile;
+    // dQ leaves through TMA reduce-add.  The two warps (qd, qt) and (qd, qt ^ 1) hold rows [32 qd, +32) x head-dim
+    // columns [32 (qt >> 1), +32) of it: as fp32 that is a 32 x 128 B swizzled box = exactly the 4 KB of the dS
+    // buffer that only these two warps ever write (each thread stages into the bytes of its own dS chunks), so the
+    // staging needs no shared memory of its own and only a 64-thread named barrier.
+    const int pair_bar = 1 + qd * 2 + (qt >> 1);
+    const bool dq_leader = (qt & 1) == 0 && lane == 0;
+    uint8_t* const dq_stage0 = smem + BwdSmem::kdS + (qt >> 1) * kTile + qd * 4096;
 
     uint32_t I0 = 0;
     int ti = 0;
@@ -716,27 +731,29 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const int hd = bh % p.H, row_base = (bh / p.H) * p.S;
       const int niter = nq - j;
 
-      // dQ of pair I (local q block `it`) -> fp32 accumulator in global memory
+      // dQ of pair I (local q block `it`) -> fp32 accumulator in global memory.  dq_full(I) also says the MMAs that
+      // read P~ / dS buffer I&1 are done, so that dS buffer is free to stage the tile until pair I+2 writes it.
+      // Rows past the end of the sequence carry dS = 0 (their probabilities are 0), so the whole box may be added.
       auto drain_dq = [&](uint32_t I, int it) {
-        const int qrow = (j + it) * kBlk + r;
         mbar_wait(&dq_full[I & 1], (I >> 1) & 1);
         tc_fence_after();
-        float* dst = p.dq_accum + size_t(row_base + qrow) * h + hd * kD + qt * 16;
         uint32_t v[16];
         __syncwarp();
         tmem_ld_32x32b_x16(tdQ + (I & 1) * 64 + lane_off + qt * 16, v);
         tmem_ld_wait();
-        if (qrow < p.S) {
-#pragma unroll
-          for (int g = 0; g < 4; ++g)
-            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(dst + g * 4),
-                         "f"(__uint_as_float(v[g * 4 + 0])), "f"(__uint_as_float(v[g * 4 + 1])),
-                         "f"(__uint_as_float(v[g * 4 + 2])), "f"(__uint_as_float(v[g * 4 + 3]))
-                         : "memory");
-        }
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(&dq_free[I & 1]);
+        const uint32_t ds_sub = ds_sub0 + (I & 1) * kPTile;
+#pragma unroll
+        for (int g = 0; g < 4; ++g)
+          st_shared_v4(swz(ds_sub, r, (qt & 1) * 4 + g), v[g * 4 + 0], v[g * 4 + 1], v[g * 4 + 2], v[g * 4 + 3]);
+        fence_proxy_async_smem();
+        named_bar_sync(pair_bar, 64);
+        if (dq_leader) {
+          tma_reduce_add_2d(&tm_dq, dq_stage0 + (I & 1) * kPTile, hd * kD + (qt >> 1) * 32, row_base + (j + it) * kBlk + qd * 32);
+          tma_store_commit();
+        }
       };
 
       // per-row statistics are fetched one block ahead so their global-load latency hides under the math
@@ -744,7 +761,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
       const float* delta_bh = p.delta + size_t(bh) * p.S;
       float lse_nx = 0.f, dl_nx = 0.f;
       if (j * kBlk + r < p.S) { lse_nx = lse_bh[j * kBlk + r]; dl_nx = delta_bh[j * kBlk + r]; }
-      // Pair I writes P~/dS buffer I&1; the MMAs of pair I-2 that read it have completed because dQ(I-2)
+      // Pair I writes dS buffer I&1; the MMAs of pair I-2 that read it have completed because dQ(I-2)
       // was drained (dq_full covers every earlier MMA) during pair I-1.  The drain of dQ(I-1) comes AFTER
       // this pair's element-wise work so its MMAs run underneath that work.
       for (int it = 0; it < niter; ++it) {
@@ -759,7 +776,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const unsigned long long grp_row = ((unsigned long long)bh * p.S + qrow) * p.S16;
         mbar_wait(sdp_full, I & 1);
         tc_fence_after();
-        const uint32_t p_sub = p_sub0 + (I & 1) * kPTile, ds_sub = ds_sub0 + (I & 1) * kPTile;
+        const uint32_t p_sub = p_sub0, ds_sub = ds_sub0 + (I & 1) * kPTile;
         // With q = 1/(1-p):  P~ = keep ? q P : 0  and  dS = P (dP~ - delta) / sqrt(d),  dP~ = keep ? q dP : 0.
         // Folding q into the exponent gives qP from one FFMA + MUFU, and
         //   dS = qP * (keep ? dP/sqrt(d) - c : -c),  c = delta (1-p) / sqrt(d)
@@ -815,6 +832,11 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
               pd[e + 1] = __uint_as_float(__float_as_uint(qp1) & m1);
             }
             const int cc = (qt & 1) * 4 + g;
+            if (g == 0) {   // the reduce-add of dQ(I-2) has finished reading this dS buffer, dV(I-1) has read P~
+              if (dq_leader) tma_store_wait_read<0>();
+              named_bar_sync(pair_bar, 64);
+              mbar_wait(p_free, (I & 1) ^ 1);
+            }
             st_shared_v4(swz(p_sub, r, cc), pack_bf16x2(pd[0], pd[1]), pack_bf16x2(pd[2], pd[3]),
                          pack_bf16x2(pd[4], pd[5]), pack_bf16x2(pd[6], pd[7]));
             st_shared_v4(swz(ds_sub, r, cc), pack_bf16x2(ds[0], ds[1]), pack_bf16x2(ds[2], ds[3]),
@@ -865,6 +887,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     }
   }
 
+  if (warp >= 2 && (((warp - 2) >> 2) & 1) == 0 && lane == 0) tma_store_wait<0>();   // dQ reduce-adds have left shared memory
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -935,6 +958,9 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
   if (rc) return rc;
   rc = make_tmap_2d_bf16(&tm_do, dout, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 64, kBlk);
   if (rc) return rc;
+  CUtensorMap tm_dq;   // fp32 dQ accumulator, 32 x 32 boxes for the reduce-add
+  rc = make_tmap_2d_sw128(&tm_dq, dq_accum, 4, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 32);
+  if (rc) return rc;
   cudaStream_t s = STREAM(stream);
   const long long nd = rows * heads;
   if (rope_cos != nullptr) {
@@ -957,7 +983,7 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
   }
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
   dim3 grid(tiles < sm_count() ? tiles : sm_count());
-  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
+  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, tm_dq, p);
   B200_CHECK_CUDA(cudaGetLastError());
   if (rope_cos != nullptr) {
     const long long nt = rows * 2 * heads * 4;
@@ -1059,6 +1085,9 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   if (rc) return rc;
   rc = make_tmap_2d_bf16(&tm_do, dout, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 64, kBlk);
   if (rc) return rc;
+  CUtensorMap tm_dq;   // the kernel reduce-adds dQ into the scratch through a tensor map (encoded on the host: no allocation)
+  rc = make_tmap_2d_sw128(&tm_dq, dq_accum, 4, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 32);
+  if (rc) return rc;
   cudaStream_t s = STREAM(stream);
   const long long nd = rows * heads;
   attn_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
@@ -1070,7 +1099,7 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
   dim3 grid(tiles < sm_count() ? tiles : sm_count());
-  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, p);
+  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, tm_dq, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);
   attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);
