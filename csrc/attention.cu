@@ -61,6 +61,7 @@ struct AttnParams {
   const float* delta;    // [B, H, S]
   float* dq_accum;       // [B*S, h] fp32
   __nv_bfloat16* dqkv;   // [B*S, 3h]
+  int tma_out;           // S % 128 == 0: output tiles (fwd O, bwd dK / dV) leave through shared memory + TMA stores
 };
 
 // 16-byte chunk `cc` (0..7) of row `row` inside a [rows][128 B] 128B-swizzled tile
@@ -108,7 +109,8 @@ struct FwdSmem {
   static constexpr int kQ = 0;                     // 2 buffers (next tile's Q lands while this one finishes)
   static constexpr int kK = kQ + 2 * kTile;        // 2 stages
   static constexpr int kV = kK + 2 * kTile;        // 2 stages
-  static constexpr int kBars = kV + 2 * kTile;     // (the probabilities never touch shared memory: they live in TMEM)
+  static constexpr int kO = kV + 2 * kTile;        // output tile staging for the TMA store
+  static constexpr int kBars = kO + kTile;         // (the probabilities never touch shared memory: they live in TMEM)
   static constexpr int kXchg = kBars + 256;                 // float [2][4][128] row-max exchange
   static constexpr int kXchgL = kXchg + 2 * 4 * 128 * 4;    // float [4][128] row-sum exchange (end of a tile)
   static constexpr int kTotal = kXchgL + 4 * 128 * 4 + 1024;
@@ -134,7 +136,7 @@ __device__ __forceinline__ int snake_tile(int r, int total) {
 }
 
 __global__ void __launch_bounds__(kAttnThreads, 1)
-attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) {
+attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_out, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + FwdSmem::kBars);
@@ -398,9 +400,28 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
       G += nkv;
       // total row sum = the four column-quarters' partial sums (same running max on all four threads)
       xchg_l[qt * 128 + r] = l;
+      const bool out_leader = qt == 0 && lane == 0;
+      if (p.tma_out && out_leader) tma_store_wait_read<0>();   // the previous tile's store has left the staging rows
       softmax_bar_sync(qd);
       l = (xchg_l[r] + xchg_l[128 + r]) + (xchg_l[256 + r] + xchg_l[384 + r]);
-      if (qrow < p.S) {
+      if (p.tma_out) {
+        // A thread's 16 output columns are 32 B of a row whose neighbours sit 2 h bytes apart: stored directly, every
+        // warp instruction touches 32 lines.  The quarter's 32 rows x 128 B go through shared memory and one TMA store.
+        const float inv = inv_keep / l;
+        const uint32_t o_tile = smem_u32(smem + FwdSmem::kO);
+#pragma unroll
+        for (int gq = 0; gq < 2; ++gq)
+          st_shared_v4(swz(o_tile, r, qt * 2 + gq),
+                       pack_bf16x2(o[gq * 8 + 0] * inv, o[gq * 8 + 1] * inv), pack_bf16x2(o[gq * 8 + 2] * inv, o[gq * 8 + 3] * inv),
+                       pack_bf16x2(o[gq * 8 + 4] * inv, o[gq * 8 + 5] * inv), pack_bf16x2(o[gq * 8 + 6] * inv, o[gq * 8 + 7] * inv));
+        if (qt == 0) p.lse[size_t(bh) * p.S + qrow] = m * kScale2 + log2f(l);
+        fence_proxy_async_smem();
+        softmax_bar_sync(qd);
+        if (out_leader) {
+          tma_store_2d(&tm_out, smem + FwdSmem::kO + qd * 4096, hd * kD, row_base + qi * kBlk + qd * 32);
+          tma_store_commit();
+        }
+      } else if (qrow < p.S) {
         const float inv = inv_keep / l;
         __nv_bfloat16* dst = p.out + size_t(row_base + qrow) * h + hd * kD + qt * 16;
 #pragma unroll
@@ -415,6 +436,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const AttnParams p) 
     }
   }
 
+  if (warp >= 2 && warp < 6 && lane == 0) tma_store_wait<0>();   // output stores have left shared memory
   tc_fence_before();
   __syncthreads();
   if (warp == 1) {
@@ -554,7 +576,7 @@ static_assert(BwdSmem::kTotal <= 227 * 1024, "backward smem exceeds the 227 KB p
 // those two counters, so nothing is re-initialised between tiles.
 __global__ void __launch_bounds__(kAttnThreads, 1)
 attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constant__ CUtensorMap tm_do,
-                const __grid_constant__ CUtensorMap tm_dq, const AttnParams p) {
+                const __grid_constant__ CUtensorMap tm_dq, const __grid_constant__ CUtensorMap tm_dkv, const AttnParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + BwdSmem::kBars);
@@ -583,6 +605,7 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
     tma_prefetch_desc(&tm_qkv);
     tma_prefetch_desc(&tm_do);
     tma_prefetch_desc(&tm_dq);
+    tma_prefetch_desc(&tm_dkv);
     mbar_init(kv_full, 1);
     mbar_init(kv_empty, 1);
     for (int i = 0; i < 3; ++i) {
@@ -866,7 +889,32 @@ attn_bwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(acc_free);   // accumulators are in registers: the next tile may start
-        if (kvrow < p.S) {
+        if (p.tma_out) {
+          // dK -> first half of the (now idle) P~ buffer, dV -> second half, as 128B-swizzled [128][64] bf16 tiles; the
+          // four warps of a row quarter meet, then one thread stores the quarter's dK rows and another its dV rows
+          // (the same threads that own those rows' later P~ writes wait for the store's read: see the pair barrier)
+          const uint32_t dk_tile = smem_u32(smem + BwdSmem::kP), dv_tile = dk_tile + kTile;
+#pragma unroll
+          for (int g = 0; g < 2; ++g) {
+            st_shared_v4(swz(dk_tile, r, qt * 2 + g),
+                         pack_bf16x2(__uint_as_float(kv_[g * 8 + 0]), __uint_as_float(kv_[g * 8 + 1])),
+                         pack_bf16x2(__uint_as_float(kv_[g * 8 + 2]), __uint_as_float(kv_[g * 8 + 3])),
+                         pack_bf16x2(__uint_as_float(kv_[g * 8 + 4]), __uint_as_float(kv_[g * 8 + 5])),
+                         pack_bf16x2(__uint_as_float(kv_[g * 8 + 6]), __uint_as_float(kv_[g * 8 + 7])));
+            st_shared_v4(swz(dv_tile, r, qt * 2 + g),
+                         pack_bf16x2(__uint_as_float(vv_[g * 8 + 0]), __uint_as_float(vv_[g * 8 + 1])),
+                         pack_bf16x2(__uint_as_float(vv_[g * 8 + 2]), __uint_as_float(vv_[g * 8 + 3])),
+                         pack_bf16x2(__uint_as_float(vv_[g * 8 + 4]), __uint_as_float(vv_[g * 8 + 5])),
+                         pack_bf16x2(__uint_as_float(vv_[g * 8 + 6]), __uint_as_float(vv_[g * 8 + 7])));
+          }
+          fence_proxy_async_smem();
+          named_bar_sync(9 + qd, 128);
+          if (dq_leader) {   // qt = 0 stores dK (P~ sub-tile 0), qt = 2 stores dV (sub-tile 1)
+            tma_store_2d(&tm_dkv, smem + BwdSmem::kP + (qt >> 1) * kTile + qd * 4096, (1 + (qt >> 1)) * h + hd * kD,
+                         row_base + j * kBlk + qd * 32);
+            tma_store_commit();
+          }
+        } else if (kvrow < p.S) {
 #pragma unroll
           for (int g = 0; g < 2; ++g) {
             *reinterpret_cast<uint4*>(dk_dst + g * 8) = make_uint4(
@@ -914,6 +962,10 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S16 = (seq + 15) / 16; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.out = (__nv_bfloat16*)out; p.lse = lse;
+  p.tma_out = seq % kBlk == 0;
+  CUtensorMap tm_out;   // 32-row boxes of the output (only used when whole tiles are in range)
+  rc = make_tmap_2d_bf16(&tm_out, out, (uint64_t)h, (uint64_t)batch * seq, (uint64_t)h, 64, 32);
+  if (rc) return rc;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   if (!configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, FwdSmem::kTotal));
@@ -922,7 +974,7 @@ int b200_attn_fwd(const void* qkv, void* out, float* lse, int batch, int seq, in
   // persistent: one CTA per SM walks its share of the (q tile, head, batch) list
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;
   dim3 grid(tiles < sm_count() ? tiles : sm_count());
-  attn_fwd_kernel<<<grid, kAttnThreads, FwdSmem::kTotal, STREAM(stream)>>>(tm, p);
+  attn_fwd_kernel<<<grid, kAttnThreads, FwdSmem::kTotal, STREAM(stream)>>>(tm, tm_out, p);
   B200_CHECK_CUDA(cudaGetLastError());
   return 0;
 }
@@ -961,6 +1013,9 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
   CUtensorMap tm_dq;   // fp32 dQ accumulator, 32 x 32 boxes for the reduce-add
   rc = make_tmap_2d_sw128(&tm_dq, dq_accum, 4, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 32);
   if (rc) return rc;
+  CUtensorMap tm_dkv;  // 32-row boxes of the dK / dV columns of dqkv
+  rc = make_tmap_2d_bf16(&tm_dkv, dqkv, 3 * (uint64_t)h, (uint64_t)rows, 3 * (uint64_t)h, 64, 32);
+  if (rc) return rc;
   cudaStream_t s = STREAM(stream);
   const long long nd = rows * heads;
   if (rope_cos != nullptr) {
@@ -976,6 +1031,7 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S16 = (seq + 15) / 16; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
+  p.tma_out = seq % kBlk == 0;
   static bool configured[kMaxDevices] = {};   // the attribute is per device
   if (!configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(attn_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, BwdSmem::kTotal));
@@ -983,7 +1039,7 @@ static int attn_bwd_impl(const void* qkv, const void* out, const void* dout, con
   }
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
   dim3 grid(tiles < sm_count() ? tiles : sm_count());
-  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, tm_dq, p);
+  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, tm_dq, tm_dkv, p);
   B200_CHECK_CUDA(cudaGetLastError());
   if (rope_cos != nullptr) {
     const long long nt = rows * 2 * heads * 4;
@@ -1088,6 +1144,9 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   CUtensorMap tm_dq;   // the kernel reduce-adds dQ into the scratch through a tensor map (encoded on the host: no allocation)
   rc = make_tmap_2d_sw128(&tm_dq, dq_accum, 4, (uint64_t)h, (uint64_t)rows, (uint64_t)h, 32);
   if (rc) return rc;
+  CUtensorMap tm_dkv;  // 32-row boxes of the dK / dV columns of dqkv
+  rc = make_tmap_2d_bf16(&tm_dkv, dqkv, 3 * (uint64_t)h, (uint64_t)rows, 3 * (uint64_t)h, 64, 32);
+  if (rc) return rc;
   cudaStream_t s = STREAM(stream);
   const long long nd = rows * heads;
   attn_delta_kernel<<<(unsigned)((nd + 255) / 256), 256, 0, s>>>((const __nv_bfloat16*)out, (const __nv_bfloat16*)dout,
@@ -1097,9 +1156,10 @@ int b200_attn_bwd_noalloc(const void* qkv, const void* out, const void* dout, co
   AttnParams p{};
   p.B = batch; p.S = seq; p.H = heads; p.S16 = (seq + 15) / 16; p.p_drop = dropout_p; p.rng = rng; p.rng_stream = rng_stream;
   p.lse = const_cast<float*>(lse); p.delta = delta; p.dq_accum = dq_accum; p.dqkv = (__nv_bfloat16*)dqkv;
+  p.tma_out = seq % kBlk == 0;
   const int tiles = ((seq + kBlk - 1) / kBlk) * heads * batch;   // persistent: one CTA per SM
   dim3 grid(tiles < sm_count() ? tiles : sm_count());
-  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, tm_dq, p);
+  attn_bwd_kernel<<<grid, kAttnThreads, BwdSmem::kTotal, s>>>(tm_qkv, tm_do, tm_dq, tm_dkv, p);
   B200_CHECK_CUDA(cudaGetLastError());
   const long long ng = rows * (h / 8);
   attn_dq_cast_kernel<<<(unsigned)((ng + 255) / 256), 256, 0, s>>>(dq_accum, (__nv_bfloat16*)dqkv, rows, h);
