@@ -182,11 +182,12 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem = *tmem_ptr;
-  const uint32_t tS[2] = {tmem + 0, tmem + 128};
-  const uint32_t tO[2] = {tmem + 256, tmem + 320};
-  // P~ (bf16, two per 32-bit column: 64 columns per 128 kv positions) is written by the softmax threads with
-  // tcgen05.st and read by the P V MMA as its A operand straight from tensor memory
-  const uint32_t tP[2] = {tmem + 384, tmem + 448};
+  // TMEM columns: S [0, 256) and O [256, 384) double buffered; P~ [384, 512) (bf16, two per 32-bit column: 64
+  // columns per 128 kv positions) is written by the softmax threads with tcgen05.st and read by the P V MMA as its A
+  // operand straight from tensor memory.  (Computed, not tabulated: an indexed array lands in local memory.)
+  auto tS = [&](int st) { return tmem + uint32_t(st) * 128u; };
+  auto tO = [&](int st) { return tmem + 256u + uint32_t(st) * 64u; };
+  auto tP = [&](int st) { return tmem + 384u + uint32_t(st) * 64u; };
 
   // Every role walks the same tile list; `ti` counts this CTA's tiles (Q buffer / phase) and `G` its kv
   // blocks across tiles (K/V stages, S/P/O buffers and their phases), so no barrier is ever re-armed.
@@ -229,7 +230,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const uint32_t k_addr = smem_u32(smem + FwdSmem::kK + st * kTile);
 #pragma unroll
         for (int t = 0; t < kD / 16; ++t)
-          umma_bf16_ss(tS[st], make_smem_desc_sw128(q_addr + t * 32, 16, 1024),
+          umma_bf16_ss(tS(st), make_smem_desc_sw128(q_addr + t * 32, 16, 1024),
                        make_smem_desc_sw128(k_addr + t * 32, 16, 1024), idesc_s, t > 0);
         tc_commit(&k_empty[st]);
         tc_commit(&s_full[st]);
@@ -244,7 +245,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         const uint32_t v_addr = smem_u32(smem + FwdSmem::kV + st * kTile);
 #pragma unroll
         for (int t = 0; t < kBlk / 16; ++t)   // A = P~ from TMEM: 16 kv positions = 8 packed columns per K step
-          umma_bf16_ts(tO[st], tP[st] + t * 8, make_smem_desc_sw128(v_addr + t * 2048, kTile, 1024), idesc_o, t > 0);
+          umma_bf16_ts(tO(st), tP(st) + t * 8, make_smem_desc_sw128(v_addr + t * 2048, kTile, 1024), idesc_o, t > 0);
         tc_commit(&v_empty[st]);
         tc_commit(&o_full[st]);
       };
@@ -302,7 +303,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         tc_fence_after();
         uint32_t v[16];
         __syncwarp();
-        tmem_ld_32x32b_x16(tO[pb] + lane_off + qt * 16, v);
+        tmem_ld_32x32b_x16(tO(pb) + lane_off + qt * 16, v);
         tmem_ld_wait();
 #pragma unroll
         for (int e = 0; e < 16; e += 2) {   // FFMA2: two accumulator lanes per issue slot
@@ -326,7 +327,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         // this thread's 32 scores stay in registers for both the max and the exp pass
         uint32_t v[32];
         __syncwarp();
-        tmem_ld_32x32b_x32(tS[st] + lane_off + qt * 32, v);
+        tmem_ld_32x32b_x32(tS(st) + lane_off + qt * 32, v);
         tmem_ld_wait();
         // The causal mask only touches the diagonal tile: a warp-uniform branch keeps the compare +
         // select out of every other tile.  Scores stay raw (unscaled) -- the 1/sqrt(d) * log2(e) factor
@@ -382,7 +383,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
 #pragma unroll
             for (int e = 0; e < 4; ++e) pk8[hf * 4 + e] = pk[e];
           }
-          tmem_st_32x32b_x8(tP[st] + lane_off + qt * 16 + g16 * 8, pk8);
+          tmem_st_32x32b_x8(tP(st) + lane_off + qt * 16 + g16 * 8, pk8);
         }
         l = l * alpha + ((l2[0].x + l2[0].y) + (l2[1].x + l2[1].y));
         tmem_st_wait();
