@@ -2,6 +2,7 @@
 // memory), fused AdamW with bf16 shadow write, gradient-norm partials, clip coefficient, RNG bump.
 #include <cuda_bf16.h>
 #include <math.h>
+#include <stdlib.h>
 
 #include "../include/b200_trainer.h"
 #include "common/host.h"
@@ -138,6 +139,157 @@ ce_fwd_bwd_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict_
   }
 }
 
+// Persistent, pipelined variant (used when two rows fit in shared memory: ld <= ~57k).  One CTA per SM walks rows
+// blockIdx.x, + gridDim.x, ...; a producer warp fetches whole rows with 1-D bulk copies (global -> smem behind an
+// mbarrier) into two row buffers, always one row ahead, while 31 consumer warps run the three passes on the row that
+// has landed and write the gradient straight to global memory (coalesced 16-byte stores).  The one-CTA-per-row
+// kernel above keeps HBM idle while a CTA computes (66 % of copy bandwidth at the benchmark shape); here the next
+// row's load is in flight during every pass.  (Also storing by bulk copy from the row buffer was measured: the next
+// load then waits for the store to drain the buffer, 172 us per chunk against 186 for the kernel above.)
+constexpr int kCeConsumers = 992;   // 31 warps + the producer warp = 1024 threads
+constexpr int kCePipeThreads = kCeConsumers + 32;
+
+// reduction over the consumer threads only (named barrier 1); `scratch` alternates between two arrays so one barrier
+// per reduction is enough
+__device__ __forceinline__ float ce_consumer_reduce(float v, float* scratch, bool is_max) {
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = is_max ? fmaxf(v, t) : v + t;
+  }
+  if (lane == 0) scratch[wid] = v;
+  named_bar_sync(1, kCeConsumers);
+  v = lane < kCeConsumers / 32 ? scratch[lane] : (is_max ? -INFINITY : 0.f);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const float t = __shfl_xor_sync(0xffffffffu, v, o);
+    v = is_max ? fmaxf(v, t) : v + t;
+  }
+  return v;
+}
+
+__global__ void __launch_bounds__(kCePipeThreads, 1)
+ce_fwd_bwd_pipe_kernel(__nv_bfloat16* __restrict__ logits, const int64_t* __restrict__ labels, float* __restrict__ loss_sum,
+                       int vocab, int ld, int rows, float loss_scale, float grad_scale) {
+  extern __shared__ __align__(128) uint8_t ce_smem[];
+  __shared__ __align__(8) uint64_t full[2], done[2];
+  __shared__ float red_a[32], red_b[32];
+  __shared__ float s_xl;
+  const uint32_t row_bytes = uint32_t(ld) * 2u;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(&full[i], 1);
+      mbar_init(&done[i], kCeConsumers / 32);
+    }
+    fence_barrier_init();
+  }
+  __syncthreads();
+  const int mine = (rows - int(blockIdx.x) + int(gridDim.x) - 1) / int(gridDim.x);   // rows this CTA processes
+
+  if (warp == kCeConsumers / 32) {
+    // ------------------------------------------------------------------ producer warp: one thread fetches the rows
+    if (lane == 0) {
+      for (int k = 0; k < mine; ++k) {
+        const int b = k & 1;
+        const size_t row = size_t(blockIdx.x) + size_t(k) * gridDim.x;
+        if (k >= 2) mbar_wait(&done[b], ((k - 2) >> 1) & 1);   // the consumers have finished with row k-2 in this buffer
+        mbar_expect_tx(&full[b], row_bytes);
+        // a few copies per row rather than one
+        constexpr uint32_t kPiece = 16384;
+        for (uint32_t off = 0; off < row_bytes; off += kPiece) {
+          const uint32_t n = row_bytes - off < kPiece ? row_bytes - off : kPiece;
+          bulk_load_g2s(smem_u32(ce_smem + size_t(b) * row_bytes) + off, reinterpret_cast<const uint8_t*>(logits + row * ld) + off, n, &full[b]);
+        }
+      }
+    }
+    return;
+  }
+
+  // -------------------------------------------------------------------- consumer warps
+  // Instruction-issue bound before HBM (19 instructions per element with scalar fp32 math: 172 us per chunk), so the
+  // passes use packed operations: bf16x2 max on the raw words, f32x2 FFMA / FADD around the one MUFU per element, and a
+  // bf16x2 product for the gradient with 1/sum split into a bf16 head and tail (one rounding, like the scalar path).
+  const int nvec = ld / 8;
+  constexpr float kLog2e = 1.4426950408889634f;
+  auto as_bf162 = [](uint32_t u) { return *reinterpret_cast<const __nv_bfloat162*>(&u); };
+  auto as_u32 = [](__nv_bfloat162 v) { return *reinterpret_cast<const uint32_t*>(&v); };
+  for (int k = 0; k < mine; ++k) {
+    const int b = k & 1;
+    const size_t row = size_t(blockIdx.x) + size_t(k) * gridDim.x;
+    const long long label = labels[row];
+    uint4* srow = reinterpret_cast<uint4*>(ce_smem + size_t(b) * row_bytes);
+    const __nv_bfloat16* srow_e = reinterpret_cast<const __nv_bfloat16*>(srow);
+    uint4* grow = reinterpret_cast<uint4*>(logits + row * ld);
+    mbar_wait(&full[b], (k >> 1) & 1);
+    if (label < 0 || label >= vocab) {   // ignored position: zero gradient, no loss
+      for (int i = threadIdx.x; i < nvec; i += kCeConsumers) grow[i] = make_uint4(0, 0, 0, 0);
+    } else {
+      const int lab_vec = int(label >> 3);
+      const bool lab_mine = lab_vec % kCeConsumers == int(threadIdx.x);   // this thread's vectors include the label's
+      // Pass 1: row max; padding columns [vocab, ld) become -inf in place so the later passes carry no bounds checks
+      __nv_bfloat162 m2[2] = {as_bf162(0xFF80FF80u), as_bf162(0xFF80FF80u)};
+      for (int i = threadIdx.x; i < nvec; i += kCeConsumers) {
+        uint4 q = srow[i];
+        if (i * 8 + 8 > vocab) {
+          uint32_t w[4] = {q.x, q.y, q.z, q.w};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            const int c = i * 8 + 2 * e;
+            if (c >= vocab) w[e] = (w[e] & 0xFFFF0000u) | 0xFF80u;
+            if (c + 1 >= vocab) w[e] = (w[e] & 0x0000FFFFu) | 0xFF800000u;
+          }
+          q = make_uint4(w[0], w[1], w[2], w[3]);
+          srow[i] = q;
+        }
+        m2[0] = __hmax2(m2[0], as_bf162(q.x));
+        m2[1] = __hmax2(m2[1], as_bf162(q.y));
+        m2[0] = __hmax2(m2[0], as_bf162(q.z));
+        m2[1] = __hmax2(m2[1], as_bf162(q.w));
+      }
+      if (lab_mine) s_xl = __bfloat162float(srow_e[label]);   // before pass 2 overwrites the logits with exponentials
+      const float2 mf = unpack_bf16x2(as_u32(__hmax2(m2[0], m2[1])));
+      const float mx = ce_consumer_reduce(fmaxf(mf.x, mf.y), red_a, true);
+      const float neg_mxs = -mx * kLog2e;
+      // Pass 2: exponentials (one FFMA2 per pair + one MUFU per element), summed in fp32, written back as bf16
+      float2 s2[2] = {make_float2(0.f, 0.f), make_float2(0.f, 0.f)};
+      const float2 l2 = make_float2(kLog2e, kLog2e), n2 = make_float2(neg_mxs, neg_mxs);
+      for (int i = threadIdx.x; i < nvec; i += kCeConsumers) {
+        const uint4 q = srow[i];
+        const uint32_t w[4] = {q.x, q.y, q.z, q.w};
+        uint32_t o[4];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 arg = ffma2(unpack_bf16x2(w[e]), l2, n2);
+          const float2 ex = make_float2(ex2_approx_ftz(arg.x), ex2_approx_ftz(arg.y));
+          s2[e & 1] = fadd2(s2[e & 1], ex);
+          o[e] = pack_bf16x2(ex.x, ex.y);
+        }
+        srow[i] = make_uint4(o[0], o[1], o[2], o[3]);
+      }
+      const float sum = ce_consumer_reduce((s2[0].x + s2[0].y) + (s2[1].x + s2[1].y), red_b, false);   // (its barrier also publishes s_xl)
+      const float inv = grad_scale / sum;
+      if (threadIdx.x == 0) atomicAdd(loss_sum, (logf(sum) + mx - s_xl) * loss_scale);
+      // Pass 3: gradient softmax * grad_scale written over the logits in global memory; the label's element (minus
+      // grad_scale) is fixed up in fp32 by the thread that wrote its vector
+      const __nv_bfloat16 ih = __float2bfloat16_rn(inv), il = __float2bfloat16_rn(inv - __bfloat162float(ih));
+      const __nv_bfloat162 ih2 = __halves2bfloat162(ih, ih), il2 = __halves2bfloat162(il, il);
+      for (int i = threadIdx.x; i < nvec; i += kCeConsumers) {
+        const uint4 q = srow[i];
+        grow[i] = make_uint4(as_u32(__hfma2(as_bf162(q.x), ih2, __hmul2(as_bf162(q.x), il2))),
+                             as_u32(__hfma2(as_bf162(q.y), ih2, __hmul2(as_bf162(q.y), il2))),
+                             as_u32(__hfma2(as_bf162(q.z), ih2, __hmul2(as_bf162(q.z), il2))),
+                             as_u32(__hfma2(as_bf162(q.w), ih2, __hmul2(as_bf162(q.w), il2))));
+      }
+      if (lab_mine)
+        reinterpret_cast<__nv_bfloat16*>(grow)[label] = __float2bfloat16_rn(__bfloat162float(srow_e[label]) * inv - grad_scale);
+    }
+    __syncwarp();   // every lane has read its part of the row: the buffer may take row k+2
+    if (lane == 0) mbar_arrive(&done[b]);
+  }
+}
+
 // ------------------------------------------------------------------------------------------------ AdamW
 // torch.optim.AdamW math (decoupled decay; denom = sqrt(v)/sqrt(bc2) + eps), 4 elements per thread.
 __global__ void __launch_bounds__(256)
@@ -216,6 +368,19 @@ int b200_ce_fwd_bwd(void* logits, const int64_t* labels, float* loss_sum, int ro
   B200_REQUIRE(ld % 8 == 0 && ld >= vocab, "ce: ld must be a multiple of 8 and >= vocab");
   const size_t smem = size_t(ld) * 2;
   B200_REQUIRE(smem <= 200 * 1024, "ce: a row of %d logits does not fit in shared memory", ld);
+  // two rows fit (and there are rows to pipeline): the persistent kernel with bulk-copy row movement
+  static const int env_pipe = [] { const char* e = getenv("B200_CE_PIPE"); return e ? atoi(e) : 1; }();
+  if (env_pipe && 2 * smem + 1024 <= 227 * 1024 && rows >= 2 * sm_count()) {
+    static size_t configured_pipe[kMaxDevices] = {};
+    if (2 * smem > configured_pipe[current_device()]) {
+      B200_CHECK_CUDA(cudaFuncSetAttribute(ce_fwd_bwd_pipe_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(2 * smem)));
+      configured_pipe[current_device()] = 2 * smem;
+    }
+    ce_fwd_bwd_pipe_kernel<<<sm_count(), kCePipeThreads, 2 * smem, STREAM(stream)>>>((__nv_bfloat16*)logits, labels, loss_sum,
+                                                                                      vocab, ld, rows, loss_scale, grad_scale);
+    B200_CHECK_CUDA(cudaGetLastError());
+    return 0;
+  }
   static size_t configured[kMaxDevices] = {};   // the attribute is per device
   if (smem > configured[current_device()]) {
     B200_CHECK_CUDA(cudaFuncSetAttribute(ce_fwd_bwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

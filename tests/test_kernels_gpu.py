@@ -66,18 +66,19 @@ def test_embedding_fwd_bwd():
     assert (dw - ref).abs().max().item() < 1e-3
 
 
-@pytest.mark.parametrize("vocab", [50257, 1000])
-def test_cross_entropy_fwd_bwd(vocab):
+@pytest.mark.parametrize("vocab,rows", [(50257, 96), (1000, 96), (50257, 1000), (1000, 777)])
+def test_cross_entropy_fwd_bwd(vocab, rows):
+    """rows < 2 x SMs: one CTA per row; more rows: the persistent kernel whose producer warp moves rows by bulk copy."""
     from distributed_llm_trainer_b200.ops import kernels as k
 
     torch.manual_seed(2)
-    rows = 96
     ld = (vocab + 127) // 128 * 128
     logits = torch.zeros(rows, ld, device="cuda", dtype=torch.bfloat16)
     logits[:, :vocab] = (torch.randn(rows, vocab, device="cuda") * 3).to(torch.bfloat16)
     logits[:, vocab:] = 77.0  # garbage in the padding must be ignored
     labels = torch.randint(0, vocab, (rows,), device="cuda")
     labels[5] = -100
+    labels[rows - 1] = -100
     ref_in = logits[:, :vocab].float().clone().requires_grad_(True)
     ref_loss = torch.nn.functional.cross_entropy(ref_in, labels, ignore_index=-100, reduction="sum")
     ref_loss.backward()
@@ -87,7 +88,7 @@ def test_cross_entropy_fwd_bwd(vocab):
     assert abs(loss.item() - ref_loss.item()) < 1e-3 * abs(ref_loss.item())
     assert (logits[:, :vocab].float() - ref_in.grad).abs().max().item() < 1e-2
     assert logits[:, vocab:].abs().max().item() == 0
-    assert logits[5].abs().max().item() == 0
+    assert logits[5].abs().max().item() == 0 and logits[rows - 1].abs().max().item() == 0
 
 
 def test_adamw_matches_torch():
