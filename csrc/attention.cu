@@ -371,14 +371,15 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tm_qkv, const __grid_constan
         alpha_prev = alpha;
         m = m_use;
       }
-      fold_o(G + nkv - 1, alpha_prev);
-      G += nkv;
-      // total row sum = the four column-quarters' partial sums (same running max on all four threads)
+      // total row sum = the four column-quarters' partial sums (same running max on all four threads); exchanged
+      // while the last P V product is still running, then that product is folded in
       xchg_l[qt * 128 + r] = l;
       const bool out_leader = qt == 0 && lane == 0;
       if (p.tma_out && out_leader) tma_store_wait_read<0>();   // the previous tile's store has left the staging rows
       softmax_bar_sync(qd);
       l = (xchg_l[r] + xchg_l[128 + r]) + (xchg_l[256 + r] + xchg_l[384 + r]);
+      fold_o(G + nkv - 1, alpha_prev);
+      G += nkv;
       if (p.tma_out) {
         // A thread's 16 output columns are 32 B of a row whose neighbours sit 2 h bytes apart: stored directly, every
         // warp instruction touches 32 lines.  The quarter's 32 rows x 128 B go through shared memory and one TMA store.
