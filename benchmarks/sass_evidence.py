@@ -27,6 +27,7 @@ LISTINGS = [
     ("attn_fwd", "attn_fwd_kernel", None),
     ("attn_bwd", "attn_bwd_kernel", None),
     ("ce_fwd_bwd", "ce_fwd_bwd_kernel", None),
+    ("ce_fwd_bwd_pipe", "ce_fwd_bwd_pipe_kernel", None),
     ("adamw_chunks_multimem", "adamw_chunks_kernel", None),
     ("pull_reduce_chunks_multimem", "pull_reduce_chunks_kernel", None),
     ("embed_bwd_rs", "embed_bwd_rs_kernel", None),
