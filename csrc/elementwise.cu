@@ -4,6 +4,7 @@
 // (B200_EPI_ROPE_BF16 / RESID_DROPOUT / SWIGLU*) the kernel here is the unfused companion used for
 // validation and for the layouts the epilogues do not cover.
 #include <cuda_bf16.h>
+#include <stdlib.h>
 
 #include "../include/b200_trainer.h"
 #include "common/host.h"
@@ -223,6 +224,85 @@ rmsnorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict
   for (int i = threadIdx.x; i < hidden; i += blockDim.x) atomicAdd(&dw[i], s_dw[i]);
 }
 
+// Same math with R = hidden / 256 warps per row, ONE vector of 8 columns per lane (used when hidden is a multiple of
+// 256 and R <= 4): 20 registers of row data per thread instead of 20 x NV, so ~64 registers and four times the
+// warps per SM of the kernel above (128 registers, 16 warps per SM: 24 % of the warp slots, 4.1 TB/s) -- while one
+// row's warps wait for their loads, others compute or store.  The R partial dot products meet in shared memory behind a
+// 32 R-thread named barrier per row (two slots, alternating, so one barrier is enough).
+constexpr int kSplitGroups = 4;   // rows in flight per CTA
+template <int R>
+__global__ void __launch_bounds__(32 * R * kSplitGroups, R <= 3 ? 3 : 2)
+rmsnorm_bwd_split_kernel(const __nv_bfloat16* __restrict__ dy, const float* __restrict__ x,
+                         const __nv_bfloat16* __restrict__ w, const float* __restrict__ rstd, float* __restrict__ dx,
+                         float* __restrict__ dw, int rows, int hidden, __nv_bfloat16* __restrict__ dy_next, float p_next,
+                         const unsigned long long* __restrict__ rng, uint32_t rng_stream) {
+  extern __shared__ float s_dw[];  // [hidden]
+  __shared__ float s_dot[2][kSplitGroups][R];
+  for (int i = threadIdx.x; i < hidden; i += blockDim.x) s_dw[i] = 0.f;
+  __syncthreads();
+  const int wid = threadIdx.x >> 5, lane = lane_id();
+  const int grp = wid / R, wr = wid - grp * R;      // row group inside the CTA, warp inside the row
+  const int i = wr * 32 + lane;                     // this lane's vector (8 columns) of every row
+  const int nvec = hidden / 8;
+  const uint4 wq = reinterpret_cast<const uint4*>(w)[i];
+  const uint32_t wqw[4] = {wq.x, wq.y, wq.z, wq.w};
+  float acc[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) acc[e] = 0.f;
+  const float inv_h = 1.f / float(hidden);
+  const float inv_keep = p_next > 0.f ? 1.f / (1.f - p_next) : 1.f;
+  int it = 0;
+  for (int row = blockIdx.x * kSplitGroups + grp; row < rows; row += gridDim.x * kSplitGroups, ++it) {
+    const uint4 dq = reinterpret_cast<const uint4*>(dy + size_t(row) * hidden)[i];
+    const float4* xr = reinterpret_cast<const float4*>(x + size_t(row) * hidden);
+    float4* dxr = reinterpret_cast<float4*>(dx + size_t(row) * hidden);
+    const float4 xa = xr[2 * i], xb = xr[2 * i + 1];
+    float4 oa = dxr[2 * i], ob = dxr[2 * i + 1];
+    const float r = rstd[row];
+    const float xs[8] = {xa.x, xa.y, xa.z, xa.w, xb.x, xb.y, xb.z, xb.w};
+    const uint32_t dqw[4] = {dq.x, dq.y, dq.z, dq.w};
+    float g[8];   // dy * w
+    float dot = 0.f;
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      const float2 d2 = unpack_bf16x2(dqw[e]), w2 = unpack_bf16x2(wqw[e]);
+      g[2 * e] = d2.x * w2.x;
+      g[2 * e + 1] = d2.y * w2.y;
+      dot += g[2 * e] * xs[2 * e] + g[2 * e + 1] * xs[2 * e + 1];
+      acc[2 * e] += d2.x * xs[2 * e] * r;
+      acc[2 * e + 1] += d2.y * xs[2 * e + 1] * r;
+    }
+    dot = warp_sum(dot);
+    if (R > 1) {
+      if (lane == 0) s_dot[it & 1][grp][wr] = dot;
+      asm volatile("bar.sync %0, %1;" ::"r"(grp + 1), "n"(32 * R) : "memory");
+      dot = 0.f;
+#pragma unroll
+      for (int t = 0; t < R; ++t) dot += s_dot[it & 1][grp][t];
+    }
+    const float coef = dot * r * r * r * inv_h;
+    float o[8] = {oa.x, oa.y, oa.z, oa.w, ob.x, ob.y, ob.z, ob.w};
+#pragma unroll
+    for (int e = 0; e < 8; ++e) o[e] += r * g[e] - xs[e] * coef;
+    dxr[2 * i] = make_float4(o[0], o[1], o[2], o[3]);
+    dxr[2 * i + 1] = make_float4(o[4], o[5], o[6], o[7]);
+    if (dy_next != nullptr) {
+      if (p_next > 0.f) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] *= inv_keep;
+        dropout_zero8(dropout_bits(rng[0], rng[1], rng_stream, (unsigned long long)row * nvec + i),
+                      dropout_threshold16(p_next) << 16, o);
+      }
+      reinterpret_cast<uint4*>(dy_next + size_t(row) * hidden)[i] =
+          make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]), pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+    }
+  }
+#pragma unroll
+  for (int e = 0; e < 8; ++e) atomicAdd(&s_dw[8 * i + e], acc[e]);
+  __syncthreads();
+  for (int c = threadIdx.x; c < hidden; c += blockDim.x) atomicAdd(&dw[c], s_dw[c]);
+}
+
 // ------------------------------------------------------------------------------------------------ dropout family
 // thread per 8-column group; group index = row * (cols/8) + col/8 (same convention as the GEMM epilogue)
 __global__ void resid_dropout_fwd_kernel(const __nv_bfloat16* __restrict__ y, const float* __restrict__ res,
@@ -433,6 +513,26 @@ int b200_rmsnorm_bwd_dropout(const void* dy, const float* x, const void* w, cons
                kNormMaxVec * 256);
   B200_REQUIRE(dy_next_ == nullptr || p_next == 0.f || rng != nullptr, "rmsnorm_bwd: rng_state required when p > 0");
   __nv_bfloat16* dy_next = (__nv_bfloat16*)dy_next_;
+  {
+    // hidden = 256 R, R <= 4: R warps per row, one vector per lane (four times the warps per SM)
+    static const int env_split = [] { const char* e = getenv("B200_NORM_SPLIT"); return e ? atoi(e) : 1; }();
+    const int R = hidden / 256;
+    if (env_split && hidden % 256 == 0 && R >= 1 && R <= 4) {
+      static const int env_grid2 = [] { const char* e = getenv("B200_NORM_GRID2"); return e ? atoi(e) : 0; }();
+      int grid2 = env_grid2 > 0 ? env_grid2 : sm_count() * (R <= 3 ? 3 : 2);   // every CTA resident
+      const int max_grid2 = (rows + kSplitGroups - 1) / kSplitGroups;
+      if (grid2 > max_grid2) grid2 = max_grid2;
+#define B200_NORM_SPLIT(RR)                                                                                         \
+  case RR:                                                                                                          \
+    rmsnorm_bwd_split_kernel<RR><<<grid2, 32 * RR * kSplitGroups, hidden * sizeof(float), STREAM(stream)>>>(          \
+        (const __nv_bfloat16*)dy, x, (const __nv_bfloat16*)w, rstd, dx, dw, rows, hidden, dy_next, p_next, rng, rng_stream); \
+    break;
+      switch (R) { B200_NORM_SPLIT(1) B200_NORM_SPLIT(2) B200_NORM_SPLIT(3) B200_NORM_SPLIT(4) }
+#undef B200_NORM_SPLIT
+      B200_CHECK_CUDA(cudaGetLastError());
+      return 0;
+    }
+  }
   int grid = sm_count() * 2;
   const int max_grid = (rows + 7) / 8;
   if (grid > max_grid) grid = max_grid;
