@@ -7,7 +7,7 @@ import torch
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("rows,hidden", [(64, 768), (1000, 1024), (333, 1600)])
+@pytest.mark.parametrize("rows,hidden", [(64, 768), (1000, 1024), (333, 1600), (130, 256), (77, 512), (4100, 768)])
 def test_rmsnorm_fwd_bwd(rows, hidden):
     from distributed_llm_trainer_b200.ops import kernels as k
     from distributed_llm_trainer_b200.ops import reference as R
