@@ -41,7 +41,11 @@ constexpr int kEpiBuf = 128 * 128;     // staging slot: 128 rows x 128 B
 // prefetch of a tile's epilogue inputs made them slower (SwiGLU' 70.5 us): these epilogues are bound by the staging
 // ring's load -> compute -> store round trip per unit, not by issue slots.  Trading one operand stage for a deeper
 // input prefetch (residual 4 units ahead, SwiGLU' 2) was slower as well (small down+resid 53.3 -> 60.4 us, SwiGLU'
-// 63.5 -> 68.5 us): the mainloop needs its 4-5 stages more than the epilogue needs the slots.
+// 63.5 -> 68.5 us): the mainloop needs its 4-5 stages more than the epilogue needs the slots.  An ablation of the
+// SwiGLU' epilogue (8192 x 3072 x 768: everything 62.5 us; no stores 56.3; no loads 52.2; no math 60.4; loads + stores
+// only 60.4; only the accumulator read 37.9) says what the two compete for: shared-memory bandwidth.  The main loop
+// moves ~80 KB per k-block through smem (TMA in, UMMA operand reads), a 64-column epilogue unit another 128 KB (TMA
+// in, LDS, STS, TMA out), together close to the 128 B/clk an SM delivers.
 constexpr int kEpiWarps = B200_EPI_WARPS;
 static_assert(kEpiWarps == 8 || kEpiWarps == 16, "8 or 16 epilogue warps");
 constexpr int kParts = kEpiWarps / 4;  // column parts of a unit (one per warp of a lane quarter)
